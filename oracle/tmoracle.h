@@ -1,0 +1,100 @@
+/* tmoracle.h — CPU oracle for the TileMotion FrameTiling / KModes hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ may be linked, imported or
+ * executed by the product path (tiler_b200/, libtmann.so).  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+ * use it, and only as the checker or the timed CPU baseline.
+ *
+ * PARITY UNPINNED: the reference (b0nefish/tiler) ships no tests, fixtures or
+ * golden vectors for this path and cannot be built here (FreePascal + Win32 +
+ * ANN.dll binary).  This is a restatement of the cited Pascal code; the
+ * known-answer vectors in tests/ are derived from that code by hand.
+ *
+ * All citations are file:line under /root/reference.
+ */
+#ifndef TMORACLE_H
+#define TMORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TMO_TILE_W 8
+#define TMO_TILE_PX 64
+#define TMO_DCT_SIZE 192        /* cTileDCTSize main.pas:38 */
+#define TMO_KM_FEATURES 80      /* cKModesFeatureCount kmodes.pas:15 */
+#define TMO_KM_SHIFT 11         /* cDissimSubMatchingSize kmodes.pas:16 */
+
+/* ---- psyv.c ---------------------------------------------------------- */
+/* RGBToYUV main.pas:2656-2679. gamma: -1 linear, 0 -> 2.0, 1 -> 0.6 (main.pas:586) */
+void tmo_rgb_to_yuv(int r, int g, int b, int gamma, double *y, double *u, double *v);
+/* WaveletGS main.pas:2805-2840 (dx=dy=8, depth=2, stride 8) */
+void tmo_wavelet_gs(const double *in, double *out, int dx, int dy, int depth);
+/* ComputeTilePsyVisFeatures main.pas:2997-3177 with UseLAB=False.
+ * rgb: 64 int32 $00BBGGRR (used when from_pal==0); palpix: 64 bytes + pal[]
+ * (used when from_pal!=0). out: 192 doubles. */
+void tmo_psyv(const int32_t *rgb, const uint8_t *palpix, const int32_t *pal,
+              int from_pal, int use_wavelets, int qweighting, int hmirror,
+              int vmirror, int gamma, double *out);
+/* batch helpers (float32 output = what crosses the FFI, main.pas:3913, 4024) */
+void tmo_psyv_queries_f32(const int32_t *rgb, int64_t nq, int use_wavelets,
+                          int gamma, float *out);
+/* stage-2 dataset rows for one palette: every tile x (vmir,hmir) in the row
+ * order of DoPsyV main.pas:3902-3905; attrs = hmir | vmir<<1. */
+void tmo_psyv_tileset_f32(const uint8_t *palpix, int64_t ntiles,
+                          const int32_t *pal, int use_wavelets, int gamma,
+                          float *out /* [ntiles*4][192] */);
+void tmo_hmirror(uint8_t *palpix);   /* main.pas:3195-3209 */
+void tmo_vmirror(uint8_t *palpix);   /* main.pas:3179-3193 */
+/* PrepareTileMirrors main.pas:4049-4069: returns hflag | vflag<<1, flips in place */
+int  tmo_prepare_tile_mirrors(uint8_t *palpix);
+/* PrepareGlobalFT main.pas:3736-3780: rows (none,H,HV,V), attrs (0,1,3,2) */
+void tmo_global_rows_f32(const uint8_t *palpix, int64_t ntiles, float *out /*[4n][64]*/,
+                         int32_t *tr_tile, uint8_t *tr_attrs);
+
+/* ---- ft_ref.c -------------------------------------------------------- */
+/* exact k-NN, squared L2, double accumulation over float32 rows; ties -> lowest
+ * index.  Also returns the (k+1)-th distance in gap2 (may be NULL) so tests
+ * can build the epsilon-gap set. */
+void tmo_knn_f64(const float *data, int64_t n, int dd, const float *q, int64_t nq,
+                 int k, int32_t *idx, double *dist, double *next_dist);
+/* float32 sequential-dimension accumulation (what ANN's annDist loop does) */
+void tmo_knn_f32(const float *data, int64_t n, int dd, const float *q, int64_t nq,
+                 int k, int32_t *idx, float *dist);
+/* timed CPU baseline: blocked brute-force 1-NN, float32, OpenMP over queries */
+void tmo_nn1_blocked_f32(const float *data, int64_t n, int dd, const float *q,
+                         int64_t nq, int32_t *idx, float *dist, int nthreads);
+int  tmo_max_threads(void);
+
+/* ---- kmodes_ref.c ---------------------------------------------------- */
+/* semantics: 0 = x86-64 asm (kmodes.pas:357-412), 1 = generic (kmodes.pas:239-250) */
+uint64_t tmo_dissim(const uint8_t *a, const uint8_t *b, int semantics);
+/* GetMinMatchingDissim kmodes.pas:316-453 / 252-270: last index wins ties */
+int32_t tmo_min_dissim(const uint8_t *rows, int64_t count, const uint8_t *item,
+                       int semantics, uint64_t *best);
+/* assignment pass kmodes.pas:984-997 */
+void tmo_kmodes_assign(const uint8_t *X, int64_t npoints, const uint8_t *centroids,
+                       int64_t k, int semantics, int32_t *clust, uint64_t *dis,
+                       int nthreads);
+/* UpdateMinDistance kmodes.pas:455-596: strict < */
+void tmo_update_min_distance(const uint8_t *X, int64_t npoints, const uint8_t *center,
+                             int semantics, uint64_t *mindist);
+/* InitFarthestFirst kmodes.pas:698-776 */
+void tmo_farthest_first(const uint8_t *X, int64_t npoints, int64_t k, int64_t init_point,
+                        int semantics, uint8_t *centroids, int64_t *chosen);
+/* WriteTileDatasetLine main.pas:4167-4183 + GetTilePalZoneThres 4142-4165 */
+int  tmo_kmodes_row(const uint8_t *palpix, int pal_size, uint8_t *row80);
+
+/* ---- gen.c ----------------------------------------------------------- */
+/* RandInt kmodes.pas:82-86 */
+uint32_t tmo_randint(uint32_t range, uint32_t *seed);
+void tmo_gen_palette(uint32_t *seed, int pal_size, int32_t *pal);
+void tmo_gen_tileset(uint32_t *seed, int64_t ntiles, int pal_size, uint8_t *palpix);
+/* queries: planted (tile,mirror) rendered through pal + noise, 1/16 pure random */
+void tmo_gen_queries(uint32_t *seed, int64_t nq, const uint8_t *palpix, int64_t ntiles,
+                     const int32_t *pal, int noise, int32_t *rgb);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,254 @@
+"""ctypes binding of the CPU oracle (oracle/libtmoracle.so).
+
+TEST INFRASTRUCTURE ONLY: importable from tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  The product path
+(tiler_b200/) never imports this module.  PARITY UNPINNED (see tmoracle.h).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def build(march="x86-64-v3", out="libtmoracle.so"):
+    subprocess.run(["make", "-s", "-C", _HERE, f"MARCH={march}", f"OUT={out}"], check=True)
+    return os.path.join(_HERE, out)
+
+
+def _load(name="libtmoracle.so"):
+    path = os.path.join(_HERE, name)
+    if not os.path.exists(path):
+        build(out=name)
+    return C.CDLL(path)
+
+
+_lib = _load()
+
+
+def use_native():
+    """Rebuild with -march=native on this machine (timed CPU baseline only)."""
+    global _lib
+    _lib = C.CDLL(build(march="native", out="libtmoracle_native.so"))
+    _proto(_lib)
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t)) if a is not None else None
+
+
+def _proto(lib):
+    lib.tmo_randint.restype = C.c_uint32
+    lib.tmo_dissim.restype = C.c_uint64
+    lib.tmo_min_dissim.restype = C.c_int32
+    lib.tmo_max_threads.restype = C.c_int
+    lib.tmo_prepare_tile_mirrors.restype = C.c_int
+    lib.tmo_kmodes_row.restype = C.c_int
+
+
+_proto(_lib)
+i64 = C.c_int64
+
+
+def max_threads():
+    return int(_lib.tmo_max_threads())
+
+
+def rgb_to_yuv(r, g, b, gamma=-1):
+    y, u, v = C.c_double(), C.c_double(), C.c_double()
+    _lib.tmo_rgb_to_yuv(int(r), int(g), int(b), int(gamma), C.byref(y), C.byref(u), C.byref(v))
+    return y.value, u.value, v.value
+
+
+def psyv(rgb=None, palpix=None, pal=None, use_wavelets=True, qweighting=False,
+         hmirror=False, vmirror=False, gamma=-1):
+    out = np.zeros(192, np.float64)
+    from_pal = rgb is None
+    if from_pal:
+        palpix = np.ascontiguousarray(palpix, np.uint8).reshape(64)
+        pal = np.ascontiguousarray(pal, np.int32)
+    else:
+        rgb = np.ascontiguousarray(rgb, np.int32).reshape(64)
+    _lib.tmo_psyv(_p(rgb, C.c_int32), _p(palpix, C.c_uint8), _p(pal, C.c_int32),
+                  int(from_pal), int(use_wavelets), int(qweighting), int(hmirror),
+                  int(vmirror), int(gamma), _p(out, C.c_double))
+    return out
+
+
+def psyv_queries_f32(rgb, use_wavelets=True, gamma=-1):
+    rgb = np.ascontiguousarray(rgb, np.int32).reshape(-1, 64)
+    out = np.empty((rgb.shape[0], 192), np.float32)
+    _lib.tmo_psyv_queries_f32(_p(rgb, C.c_int32), i64(rgb.shape[0]), int(use_wavelets),
+                              int(gamma), _p(out, C.c_float))
+    return out
+
+
+def psyv_tileset_f32(palpix, pal, use_wavelets=True, gamma=-1):
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    pal = np.ascontiguousarray(pal, np.int32)
+    out = np.empty((palpix.shape[0] * 4, 192), np.float32)
+    _lib.tmo_psyv_tileset_f32(_p(palpix, C.c_uint8), i64(palpix.shape[0]), _p(pal, C.c_int32),
+                              int(use_wavelets), int(gamma), _p(out, C.c_float))
+    return out
+
+
+def hmirror(palpix):
+    a = np.array(palpix, np.uint8).reshape(64).copy()
+    _lib.tmo_hmirror(_p(a, C.c_uint8))
+    return a.reshape(8, 8)
+
+
+def vmirror(palpix):
+    a = np.array(palpix, np.uint8).reshape(64).copy()
+    _lib.tmo_vmirror(_p(a, C.c_uint8))
+    return a.reshape(8, 8)
+
+
+def prepare_tile_mirrors(palpix):
+    a = np.array(palpix, np.uint8).reshape(64).copy()
+    f = _lib.tmo_prepare_tile_mirrors(_p(a, C.c_uint8))
+    return a.reshape(8, 8), f
+
+
+def global_rows_f32(palpix):
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    n = palpix.shape[0]
+    out = np.empty((n * 4, 64), np.float32)
+    tr_tile = np.empty(n * 4, np.int32)
+    tr_attrs = np.empty(n * 4, np.uint8)
+    _lib.tmo_global_rows_f32(_p(palpix, C.c_uint8), i64(n), _p(out, C.c_float),
+                             _p(tr_tile, C.c_int32), _p(tr_attrs, C.c_uint8))
+    return out, tr_tile, tr_attrs
+
+
+def knn_f64(data, q, k=1):
+    data = np.ascontiguousarray(data, np.float32)
+    q = np.ascontiguousarray(q, np.float32).reshape(-1, data.shape[1])
+    nq = q.shape[0]
+    idx = np.empty((nq, k), np.int32)
+    dist = np.empty((nq, k), np.float64)
+    nxt = np.empty(nq, np.float64)
+    _lib.tmo_knn_f64(_p(data, C.c_float), i64(data.shape[0]), int(data.shape[1]),
+                     _p(q, C.c_float), i64(nq), int(k), _p(idx, C.c_int32),
+                     _p(dist, C.c_double), _p(nxt, C.c_double))
+    return idx, dist, nxt
+
+
+def knn_f32(data, q, k=1):
+    data = np.ascontiguousarray(data, np.float32)
+    q = np.ascontiguousarray(q, np.float32).reshape(-1, data.shape[1])
+    nq = q.shape[0]
+    idx = np.empty((nq, k), np.int32)
+    dist = np.empty((nq, k), np.float32)
+    _lib.tmo_knn_f32(_p(data, C.c_float), i64(data.shape[0]), int(data.shape[1]),
+                     _p(q, C.c_float), i64(nq), int(k), _p(idx, C.c_int32), _p(dist, C.c_float))
+    return idx, dist
+
+
+def nn1_blocked_f32(data, q, nthreads=0):
+    data = np.ascontiguousarray(data, np.float32)
+    q = np.ascontiguousarray(q, np.float32).reshape(-1, data.shape[1])
+    nq = q.shape[0]
+    idx = np.empty(nq, np.int32)
+    dist = np.empty(nq, np.float32)
+    _lib.tmo_nn1_blocked_f32(_p(data, C.c_float), i64(data.shape[0]), int(data.shape[1]),
+                             _p(q, C.c_float), i64(nq), _p(idx, C.c_int32), _p(dist, C.c_float),
+                             int(nthreads))
+    return idx, dist
+
+
+# ---- kmodes -----------------------------------------------------------------
+ASM, GENERIC = 0, 1
+
+
+def dissim(a, b, semantics=ASM):
+    a = np.ascontiguousarray(a, np.uint8)
+    b = np.ascontiguousarray(b, np.uint8)
+    assert a.size == 80 and b.size == 80
+    return int(_lib.tmo_dissim(_p(a, C.c_uint8), _p(b, C.c_uint8), int(semantics)))
+
+
+def min_dissim(rows, item, semantics=ASM):
+    rows = np.ascontiguousarray(rows, np.uint8).reshape(-1, 80)
+    item = np.ascontiguousarray(item, np.uint8)
+    best = C.c_uint64()
+    r = _lib.tmo_min_dissim(_p(rows, C.c_uint8), i64(rows.shape[0]), _p(item, C.c_uint8),
+                            int(semantics), C.byref(best))
+    return int(r), int(best.value)
+
+
+def kmodes_assign(X, centroids, semantics=ASM, nthreads=0):
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    centroids = np.ascontiguousarray(centroids, np.uint8).reshape(-1, 80)
+    clust = np.empty(X.shape[0], np.int32)
+    dis = np.empty(X.shape[0], np.uint64)
+    _lib.tmo_kmodes_assign(_p(X, C.c_uint8), i64(X.shape[0]), _p(centroids, C.c_uint8),
+                           i64(centroids.shape[0]), int(semantics), _p(clust, C.c_int32),
+                           _p(dis, C.c_uint64), int(nthreads))
+    return clust, dis
+
+
+def update_min_distance(X, center, mindist, semantics=ASM):
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    center = np.ascontiguousarray(center, np.uint8)
+    mindist = np.ascontiguousarray(mindist, np.uint64).copy()
+    _lib.tmo_update_min_distance(_p(X, C.c_uint8), i64(X.shape[0]), _p(center, C.c_uint8),
+                                 int(semantics), _p(mindist, C.c_uint64))
+    return mindist
+
+
+def farthest_first(X, k, init_point, semantics=ASM):
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    cent = np.empty((k, 80), np.uint8)
+    chosen = np.empty(k, np.int64)
+    _lib.tmo_farthest_first(_p(X, C.c_uint8), i64(X.shape[0]), i64(k), i64(init_point),
+                            int(semantics), _p(cent, C.c_uint8), _p(chosen, C.c_int64))
+    return cent, chosen
+
+
+def kmodes_row(palpix, pal_size=16):
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(64)
+    row = np.empty(80, np.uint8)
+    r = _lib.tmo_kmodes_row(_p(palpix, C.c_uint8), int(pal_size), _p(row, C.c_uint8))
+    return row, int(r)
+
+
+def kmodes_rows(palpix, pal_size=16):
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    return np.stack([kmodes_row(t, pal_size)[0] for t in palpix])
+
+
+# ---- synthetic generators ---------------------------------------------------
+BASE_SEED = 0x42381337  # kmodes.pas:930
+
+
+def randint(rng, seed):
+    s = C.c_uint32(seed)
+    r = _lib.tmo_randint(C.c_uint32(rng), C.byref(s))
+    return int(r), int(s.value)
+
+
+def gen_palette(seed, pal_size=16):
+    s = C.c_uint32(seed)
+    pal = np.empty(pal_size, np.int32)
+    _lib.tmo_gen_palette(C.byref(s), int(pal_size), _p(pal, C.c_int32))
+    return pal, int(s.value)
+
+
+def gen_tileset(seed, ntiles, pal_size=16):
+    s = C.c_uint32(seed)
+    px = np.empty((ntiles, 64), np.uint8)
+    _lib.tmo_gen_tileset(C.byref(s), i64(ntiles), int(pal_size), _p(px, C.c_uint8))
+    return px, int(s.value)
+
+
+def gen_queries(seed, nq, palpix, pal, noise=6):
+    s = C.c_uint32(seed)
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    pal = np.ascontiguousarray(pal, np.int32)
+    rgb = np.empty((nq, 64), np.int32)
+    _lib.tmo_gen_queries(C.byref(s), i64(nq), _p(palpix, C.c_uint8), i64(palpix.shape[0]),
+                         _p(pal, C.c_int32), int(noise), _p(rgb, C.c_int32))
+    return rgb, int(s.value)
