@@ -1,0 +1,353 @@
+#!/usr/bin/env python
+"""bench.py — FrameTiling best-tile search throughput on B200 (BASELINE.json metric).
+
+A step = one pass of the hot path (query PsyV descriptor -> exact 1-NN over the
+tileset in all 4 mirrors -> result) over the whole synthetic clip of the workload:
+  N = 1 : configs[1]  720p x 300 frames, 8x8 tiles, 16k-tile set  (Q = 4 320 000, rows = 65 536)
+  N > 1 : the same clip PER GPU (weak scaling), tileset broadcast once over NCCL before
+          the timed region, per-step result gather to rank 0 inside it.
+`value`  : tile-queries/s, inputs resident in HBM, CUDA events on the launching stream.
+`e2e`    : same metric through the host-buffer C-ABI call (tm_frametiling_search):
+           pinned host RGB in, host idx/err out, copies inside the timed region.
+`--impl reference` : the reference's CPU loop (oracle port, all host threads) on a
+           bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (frames, tilemap positions per frame, tiles)
+    "c1_320x240_64f_4k": (64, 40 * 30, 4096),
+    "c2_720p_300f_16k": (300, 160 * 90, 16384),
+    "c3_1080p_1000f_64k": (1000, 240 * 135, 65536),
+}
+D = 192
+METRIC = "FrameTiling tile-queries/sec"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2_720p_300f_16k", choices=sorted(WORKLOADS))
+    ap.add_argument("--engine", default="auto", choices=["auto", "simt", "tc"])
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU-baseline sample time")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------ synthetic data (torch, on device)
+def synth_tileset(torch, ntiles, pal_size, gen):
+    """random base + linear gradient + +-1 noise per tile, like SURVEY.md §8d; palette sorted by luma"""
+    dev = gen.device
+    pal = torch.randint(0, 256, (pal_size, 3), generator=gen, device=dev)
+    luma = 2126 * pal[:, 0] + 7152 * pal[:, 1] + 722 * pal[:, 2]
+    pal = pal[torch.argsort(luma)]
+    pal_i32 = (pal[:, 0] | (pal[:, 1] << 8) | (pal[:, 2] << 16)).to(torch.int32)  # $00BBGGRR
+    base = torch.randint(0, pal_size, (ntiles, 1, 1), generator=gen, device=dev)
+    gx = torch.randint(-3, 4, (ntiles, 1, 1), generator=gen, device=dev)
+    gy = torch.randint(-3, 4, (ntiles, 1, 1), generator=gen, device=dev)
+    div = torch.randint(2, 8, (ntiles, 1, 1), generator=gen, device=dev)
+    xs = torch.arange(8, device=dev).view(1, 1, 8) - 4
+    ys = torch.arange(8, device=dev).view(1, 8, 1) - 4
+    noise = torch.randint(-1, 2, (ntiles, 8, 8), generator=gen, device=dev)
+    t = base + torch.div(gx * xs + gy * ys, div, rounding_mode="trunc") + noise
+    return t.clamp_(0, pal_size - 1).to(torch.uint8).reshape(ntiles, 64).contiguous(), pal_i32.contiguous()
+
+
+def synth_queries(torch, nq, tiles, pal_i32, gen, noise=6, chunk=1 << 20):
+    """planted (tile, mirror) rendered through the palette + uniform noise; 1/16 pure random RGB"""
+    dev = gen.device
+    out = torch.empty((nq, 64), dtype=torch.int32, device=dev)
+    t3 = tiles.view(-1, 8, 8).long()
+    pal = torch.stack([pal_i32 & 0xff, (pal_i32 >> 8) & 0xff, (pal_i32 >> 16) & 0xff], -1).long()
+    for q0 in range(0, nq, chunk):
+        c = min(chunk, nq - q0)
+        tid = torch.randint(0, tiles.shape[0], (c,), generator=gen, device=dev)
+        hm = torch.randint(0, 2, (c, 1, 1), generator=gen, device=dev).bool()
+        vm = torch.randint(0, 2, (c, 1, 1), generator=gen, device=dev).bool()
+        px = t3[tid]
+        px = torch.where(hm, px.flip(2), px)
+        px = torch.where(vm, px.flip(1), px)
+        rgb = pal[px.reshape(c, 64)] + torch.randint(-noise, noise + 1, (c, 64, 3), generator=gen, device=dev)
+        rnd = torch.randint(0, 16, (c, 1, 1), generator=gen, device=dev) == 0
+        rgb = torch.where(rnd, torch.randint(0, 256, (c, 64, 3), generator=gen, device=dev), rgb).clamp_(0, 255)
+        out[q0:q0 + c] = (rgb[..., 0] | (rgb[..., 1] << 8) | (rgb[..., 2] << 16)).to(torch.int32)
+    return out
+
+
+# ------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop, self.th = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                p = [x.strip() for x in o.strip().split(",")]
+                if len(p) >= 6:
+                    self.rows.append(p)
+            except Exception:
+                pass
+            self.stop.wait(0.2)
+
+    def __enter__(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ CPU baseline (oracle = checker / timed baseline only)
+def cpu_baseline(tiles_np, pal_np, rgb_sample_np, target_s, check_idx=None, check_err=None):
+    """The reference's DoFrameTiling loop (main.pas:4020-4038) restated in C (oracle/), timed on this
+    box's host cores on a bounded sample of the same workload; also checks the GPU result on the sample."""
+    from oracle import tmoracle as o
+    try:
+        o.use_native()
+    except Exception:
+        pass
+    cores = o.max_threads()
+    ds = o.psyv_tileset_f32(tiles_np, pal_np)  # dataset build is not timed (one-time per keyframe)
+    n = 64
+    t0 = time.perf_counter()
+    o.nn1_blocked_f32(ds, o.psyv_queries_f32(rgb_sample_np[:n]))
+    per_q = (time.perf_counter() - t0) / n
+    n = int(max(64, min(len(rgb_sample_np), target_s / max(per_q, 1e-9))))
+    t0 = time.perf_counter()
+    q = o.psyv_queries_f32(rgb_sample_np[:n])
+    idx, dist = o.nn1_blocked_f32(ds, q)
+    dt = time.perf_counter() - t0
+    out = {"value": n / dt, "unit": "tile-queries/s", "cores": cores, "kind": "port",
+           "sample": f"{n} queries (descriptor + exact 1-NN, float32 blocked brute force, OpenMP) "
+                     f"against the full {ds.shape[0]}-row dataset in {dt:.2f} s"}
+    if check_idx is not None:
+        m = min(n, len(check_idx))
+        same = int((idx[:m] == check_idx[:m]).sum())
+        rel = float(np.max(np.abs(dist[:m] - check_err[:m]) / np.maximum(dist[:m], 1e-6)))
+        out["parity_on_sample"] = {"n": m, "index_equal": same, "max_rel_dist_err": rel}
+    return out
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    import torch  # only for the synthetic generator (CPU)
+    frames, pos, ntiles = WORKLOADS[args.workload]
+    gen = torch.Generator(device="cpu").manual_seed(0x42381337)
+    tiles, pal = synth_tileset(torch, ntiles, 16, gen)
+    from oracle import tmoracle as o
+    try:
+        o.use_native()
+    except Exception:
+        pass
+    ds = o.psyv_tileset_f32(tiles.numpy(), pal.numpy())
+    rgb = synth_queries(torch, 4096, tiles, pal, gen).numpy()
+    t0 = time.perf_counter()
+    o.nn1_blocked_f32(ds, o.psyv_queries_f32(rgb[:64]))
+    per_q = (time.perf_counter() - t0) / 64
+    total = args.steps + args.warmup
+    n = int(max(64, min(4096, (120.0 / max(total, 1)) / max(per_q, 1e-9))))  # whole run <= ~2 min
+    for _ in range(args.warmup):
+        o.nn1_blocked_f32(ds, o.psyv_queries_f32(rgb[:n]))
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        o.nn1_blocked_f32(ds, o.psyv_queries_f32(rgb[:n]))
+    dt = time.perf_counter() - t0
+    v = n * args.steps / dt
+    cores = o.max_threads()
+    sample = f"{n} queries per step against the full {ds.shape[0]}-row dataset"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "tile-queries/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "queries_per_step": n, "dataset_rows": int(ds.shape[0]), "dim": D,
+                   "note": "reference CPU loop (faithful C port of DoFrameTiling, exact brute-force 1-NN); the "
+                           "FreePascal/ANN.dll original cannot be built on Linux"},
+        "cpu_baseline": {"value": v, "unit": "tile-queries/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "tile-queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------ B200 arm
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import tiler_b200 as tb
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    tb.set_device(local_rank)
+    stream = torch.cuda.current_stream()
+    tb.set_stream(stream.cuda_stream)  # library work is enqueued on torch's current stream: events see it
+    tb.set_engine({"auto": tb.ENGINE_AUTO, "simt": tb.ENGINE_SIMT, "tc": tb.ENGINE_TC}[args.engine])
+
+    frames, pos, ntiles = WORKLOADS[args.workload]
+    nq = frames * pos  # per GPU (weak scaling)
+    gen = torch.Generator(device=dev).manual_seed(0x42381337)
+    tiles, pal = synth_tileset(torch, ntiles, 16, gen)
+    if world > 1:  # one-time tileset broadcast over NCCL/NVLink; rank 0's tileset wins
+        dist.broadcast(tiles, 0)
+        dist.broadcast(pal, 0)
+    gen.manual_seed(0x42381337 + 1 + rank)
+    d_rgb = synth_queries(torch, nq, tiles, pal, gen)
+    torch.cuda.synchronize()
+    t_ds0 = time.perf_counter()
+    tree = tb.KDTree.from_tileset(tiles, pal.view(1, -1))  # pack/mirror kernel + operand prep, on device
+    torch.cuda.synchronize()
+    dataset_build_ms = 1e3 * (time.perf_counter() - t_ds0)
+    d_idx = torch.empty(nq, dtype=torch.int32, device=dev)
+    d_err = torch.empty(nq, dtype=torch.float32, device=dev)
+    gather_idx = [torch.empty_like(d_idx) for _ in range(world)] if (world > 1 and rank == 0) else None
+    gather_err = [torch.empty_like(d_err) for _ in range(world)] if (world > 1 and rank == 0) else None
+
+    def step():
+        tree.frametiling_search(d_rgb, out_idx=d_idx, out_err=d_err)
+        if world > 1:  # result gather (NCCL) is part of the step
+            dist.gather(d_idx, gather_idx, 0)
+            dist.gather(d_err, gather_err, 0)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    tb.reset_stats()
+    tb.set_profiling(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clk:
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            step()
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    st = tb.stats()
+    tb.set_profiling(False)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = world * nq * args.steps / (ms / 1e3)
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        h_rgb = torch.empty((nq, 64), dtype=torch.int32, pin_memory=True)
+        h_rgb.copy_(d_rgb)
+        h_idx = torch.empty(nq, dtype=torch.int32, pin_memory=True)
+        h_err = torch.empty(nq, dtype=torch.float32, pin_memory=True)
+        rgb_np, idx_np, err_np = h_rgb.numpy(), h_idx.numpy(), h_err.numpy()
+        e_steps = max(1, min(args.steps, 3))
+        tree.frametiling_search(rgb_np, out_idx=idx_np, out_err=err_np)  # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            tree.frametiling_search(rgb_np, out_idx=idx_np, out_err=err_np)  # synchronous: returns with results on host
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": world * nq * e_steps / dt, "unit": "tile-queries/s",
+               "h2d_bytes_per_step": int(nq * 256), "d2h_bytes_per_step": int(nq * 8), "steps": e_steps,
+               "timer": "host wall clock around the synchronous C-ABI call, max over ranks"}
+
+    if rank == 0:
+        n_rows = ntiles * 4
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        # dominant kernel = the search; algorithmic flops = 2*Q*N*D per launch
+        search_ms = st["coarse_ms"] if st["coarse_launches"] else st["search_ms"]
+        launches = st["coarse_launches"] if st["coarse_launches"] else max(1, args.steps * ((nq + (1 << 21) - 1) >> 21))
+        flops_total = 2.0 * nq * n_rows * D * args.steps
+        achieved = flops_total / (search_ms / 1e3) / 1e12 if search_ms > 0 else None
+        peak = peaks.get("bf16_tflops_sustained") or 1400.0
+        peak_src = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback"
+        line = {
+            "metric": METRIC, "value": value, "unit": "tile-queries/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f16 tensor-core coarse pass, f32 exact re-rank" if st["coarse_launches"] else "f32",
+            "data": "synthetic",
+            "config": {"workload": args.workload, "queries_per_gpu": nq, "dataset_rows": n_rows, "dim": D,
+                       "mirrors": 4, "parallelism": f"query-sharded x{world}, tileset replicated",
+                       "l2_policy": "inputs larger than L2 (query RGB %.2f GB per step)" % (nq * 256 / 1e9),
+                       "engine": args.engine, "dataset_build_ms": dataset_build_ms},
+            "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                         "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
+                         "kernel": "search (coarse tensor-core pass)" if st["coarse_launches"] else "search (exact SIMT)",
+                         "kernel_ms_per_launch": search_ms / launches, "launches": launches,
+                         "algorithmic_flops_per_launch": flops_total / launches},
+            "phases_ms_per_step": {"descriptor": st["desc_ms"] / args.steps, "search": st["search_ms"] / args.steps,
+                                   "coarse": st["coarse_ms"] / args.steps, "rerank": st["rerank_ms"] / args.steps},
+            "fallback_queries_per_step": st["fallback_queries"] / args.steps,
+            "gpu_launches": int(st["kernel_launches"]),
+            "clocks": clk.summary(),
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if not args.no_cpu_baseline and world == 1:
+            m = 1 << 15
+            line["cpu_baseline"] = cpu_baseline(tiles.cpu().numpy(), pal.cpu().numpy(), d_rgb[:m].cpu().numpy(),
+                                                args.cpu_seconds, d_idx[:m].cpu().numpy(), d_err[:m].cpu().numpy())
+        print(json.dumps(line))
+    tree.destroy()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,165 @@
+/* tmann.h — C ABI of libtmann.so, the B200 (sm_100a) replacement for the k-NN
+ * boundary of GliGli's TileMotion encoder (b0nefish/tiler).
+ *
+ * Part 1 re-exports, bit-compatibly, the five symbols the encoder imports from
+ * ANN.dll (reference extern.pas:63-67, types extern.pas:21-39).  Part 2 adds
+ * batch / fused entry points so the Pascal side can hand a whole frame (or
+ * keyframe) to the GPU per call; each cites the reference code it replaces.
+ *
+ * Conventions: plain pointers and sizes only.  Pointers named h_* are host
+ * memory, d_* are device (cudaMalloc) memory on the library's current device.
+ * Part 2 calls return 0 on success or a negative TM_E* code and never abort;
+ * tm_last_error() gives the message.  Part 1 keeps the legacy shape (no error
+ * channel: NULL handle / index -1 on failure).  There is no CPU fallback:
+ * every call fails with TM_ENODEVICE when no sm_100 device is usable.
+ */
+#ifndef TMANN_H
+#define TMANN_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define TM_API __declspec(dllexport)
+#else
+#define TM_API __attribute__((visibility("default")))
+#endif
+
+/* ---------------------------------------------------------------- Part 1 */
+/* Opaque handle; replaces PANNkdtree (extern.pas:36-39). */
+typedef struct ANNkdtree ANNkdtree;
+
+/* extern.pas:63 — pa: n row pointers of dd floats (rows need not be contiguous);
+ * bs and split are accepted and ignored (the search is exact, like eps = 0).
+ * Snapshots the rows to the device; call sites main.pas:3779 (dd=64), 3961 (dd=192). */
+TM_API ANNkdtree *ann_kdtree_create(float **pa, int n, int dd, int bs, int split);
+/* extern.pas:64 — NULL-safe; call sites main.pas:3784, 3983. */
+TM_API void ann_kdtree_destroy(ANNkdtree *akd);
+/* extern.pas:65 — exact 1-NN; returns row index (-1 on failure), *err (may be
+ * NULL) = squared L2 in float32.  eps is ignored (always exact). main.pas:4027. */
+TM_API int ann_kdtree_search(ANNkdtree *akd, float *q, float eps, float *err);
+/* extern.pas:66 — same result as ann_kdtree_search (no call site in main.pas). */
+TM_API int ann_kdtree_pri_search(ANNkdtree *akd, float *q, float eps, float *err);
+/* extern.pas:67 — cnt nearest rows ascending by squared L2; returns 0 (the
+ * reference's return value is garbage and ignored, main.pas:3830). */
+TM_API int ann_kdtree_search_multi(ANNkdtree *akd, int *idxs, float *errs, int cnt,
+                                   float *q, float eps);
+
+/* ---------------------------------------------------------------- Part 2 */
+enum {
+    TM_OK = 0,
+    TM_EINVAL = -1,    /* bad argument */
+    TM_ENODEVICE = -2, /* no usable sm_100 GPU / CUDA failure at init */
+    TM_ECUDA = -3,     /* CUDA runtime error (see tm_last_error) */
+    TM_ENOMEM = -4
+};
+
+/* tm_psyv flags: the GUI options of btnDoFrameTilingClick main.pas:962-964 */
+enum {
+    TM_PSYV_WAVELETS = 1, /* UseWavelets (default on, main.lfm:372-379); 0 = DCT-II */
+    TM_PSYV_QWEIGHT = 2   /* QWeighting (off on the FrameTiling path) */
+};
+/* KModes dissimilarity semantics */
+enum {
+    TM_KM_ASM = 0,    /* x86-64 asm that ships: kmodes.pas:357-412 */
+    TM_KM_GENERIC = 1 /* documented generic form: kmodes.pas:239-250 */
+};
+/* search engines (tm_set_engine); AUTO picks the tensor-core path when dd % 16 == 0 */
+enum { TM_ENGINE_AUTO = 0, TM_ENGINE_SIMT = 1, TM_ENGINE_TC = 2 };
+
+TM_API const char *tm_last_error(void);
+TM_API int tm_version(void);
+/* Select the CUDA device for the calling process (default: current device). */
+TM_API int tm_set_device(int device);
+TM_API int tm_set_engine(int engine);
+/* Run all library work on the caller's CUDA stream (a cudaStream_t).  From then on the
+ * *_dev entry points only enqueue work on that stream and return without synchronising;
+ * without it they synchronise the device on entry and their own stream on exit. */
+TM_API int tm_set_stream(void *cuda_stream);
+TM_API int tm_device_sync(void);
+
+/* Contiguous-row variant of ann_kdtree_create; rows may be host or device memory
+ * (is_device != 0).  Replaces the per-row gather of main.pas:3757-3779. */
+TM_API ANNkdtree *tm_dataset_create(const float *rows, int64_t n, int dd, int is_device);
+TM_API int64_t tm_dataset_rows(const ANNkdtree *akd);
+TM_API int tm_dataset_dim(const ANNkdtree *akd);
+
+/* Batch k-NN: nq queries x dd floats, contiguous; out idxs[nq*k], errs[nq*k]
+ * ascending per query.  One call replaces the per-position loop of
+ * DoFrameTiling main.pas:4020-4038 (k = 1) or UseOne main.pas:3830 (k = 8). */
+TM_API int ann_kdtree_search_batch(ANNkdtree *akd, const float *h_q, int64_t nq, int k,
+                                   int *h_idxs, float *h_errs);
+TM_API int tm_search_batch_dev(ANNkdtree *akd, const float *d_q, int64_t nq, int k,
+                               int *d_idxs, float *d_errs);
+
+/* PsyV descriptors, replaces ComputeTilePsyVisFeatures main.pas:2997-3177
+ * (UseLAB = False).  gamma: -1 linear, 0 or 1 = gGamma index (main.pas:586).
+ * Queries: 64 int32 $00BBGGRR per tile (TRGBPixels main.pas:155), FromPal = False,
+ * no mirror (main.pas:4023) -> out[nq][192] float32 (main.pas:4024-4025). */
+TM_API int tm_psyv_queries(const int32_t *h_rgb, int64_t nq, int flags, int gamma, float *h_out);
+TM_API int tm_psyv_queries_dev(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out);
+
+/* Stage-2 dataset straight from the tileset (DoPsyV main.pas:3883-3919 with every
+ * (pal, tile, vmir, hmir) used): palpix[ntiles][64] palette indices, pals[npal][pal_size]
+ * int32 colours, tile_flags[ntiles] = TTile.HMirror | VMirror<<1 (may be NULL = 0).
+ * Row r = ((p*ntiles + t)*2 + vmir)*2 + hmir; TRToAttrs = hmir | vmir<<1 (main.pas:3910). */
+TM_API ANNkdtree *tm_tileset_dataset_create(const uint8_t *h_palpix, int64_t ntiles,
+                                            const int32_t *h_pals, int npal, int pal_size,
+                                            const uint8_t *h_tile_flags, int flags, int gamma);
+TM_API ANNkdtree *tm_tileset_dataset_create_dev(const uint8_t *d_palpix, int64_t ntiles,
+                                                const int32_t *d_pals, int npal, int pal_size,
+                                                const uint8_t *d_tile_flags, int flags, int gamma);
+/* copy the dataset rows (float32) back, for inspection / parity tests */
+TM_API int tm_dataset_read(const ANNkdtree *akd, float *h_rows);
+
+/* Fused FrameTiling hot loop (main.pas:4020-4038): RGB tiles -> descriptor ->
+ * exact 1-NN in akd (dd must be 192).  out row index + squared-L2 err per query. */
+TM_API int tm_frametiling_search(ANNkdtree *akd, const int32_t *h_rgb, int64_t nq, int flags,
+                                 int gamma, int *h_idx, float *h_err);
+TM_API int tm_frametiling_search_dev(ANNkdtree *akd, const int32_t *d_rgb, int64_t nq, int flags,
+                                     int gamma, int *d_idx, float *d_err);
+
+/* Stage-1 rows of PrepareGlobalFT main.pas:3736-3780: for each tile 4 rows of 64
+ * floats in order (none, H, H+V, V); tr_tile / tr_attrs (0,1,3,2) side tables. */
+TM_API ANNkdtree *tm_global_dataset_create(const uint8_t *h_palpix, int64_t ntiles,
+                                           int32_t *h_tr_tile, uint8_t *h_tr_attrs);
+
+/* KModes assignment pass (DoGMMD kmodes.pas:825-835; loops 866-878, 984-997):
+ * clust[i] = arg-min over k centroids of the matching dissimilarity, last index
+ * wins ties (kmodes.pas:414-415); dis[i] (may be NULL) = that dissimilarity.
+ * X[npoints][80], centroids[k][80] contiguous bytes. */
+TM_API int tm_kmodes_assign(const uint8_t *h_X, int64_t npoints, const uint8_t *h_centroids,
+                            int64_t k, int semantics, int32_t *h_clust, uint64_t *h_dis);
+TM_API int tm_kmodes_assign_dev(const uint8_t *d_X, int64_t npoints, const uint8_t *d_centroids,
+                                int64_t k, int semantics, int32_t *d_clust, uint64_t *d_dis);
+/* UpdateMinDistance (kmodes.pas:455-596): mindist[i] = min(mindist[i], dissim(center, X[i])) */
+TM_API int tm_kmodes_update_min_distance(const uint8_t *h_X, int64_t npoints,
+                                         const uint8_t *h_center, int semantics,
+                                         uint64_t *h_mindist);
+
+/* counters since the last reset: kernel launches issued by this library, queries
+ * that took the exact-fallback path after the tensor-core pass, and the device
+ * time (ms, CUDA events) of the last search call split by phase. */
+typedef struct tm_stats {
+    int64_t kernel_launches;
+    int64_t queries;
+    int64_t fallback_queries;
+    /* device time (ms, CUDA events on the library's stream) accumulated since the last
+     * reset while tm_set_profiling(1) is on: descriptor kernels, whole search phase,
+     * and inside it the tensor-core coarse kernel and the FP32 re-rank. */
+    float desc_ms;
+    float search_ms;
+    float coarse_ms;
+    float rerank_ms;
+    int64_t coarse_launches;
+} tm_stats;
+/* tm_get_stats synchronises the library's stream when profiling is on. */
+TM_API int tm_set_profiling(int on);
+TM_API int tm_get_stats(tm_stats *out);
+TM_API int tm_reset_stats(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

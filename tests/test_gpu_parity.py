@@ -1,0 +1,227 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs.
+
+Bars (north_star): descriptor rows bit-exact (FP64 arithmetic in the reference's
+operation order); search index bit-exact wherever the best/second-best gap exceeds
+EPS_GAP relative, distances within RTOL of the oracle's float64 value and bit-equal
+to its float32 sequential accumulation; KModes assignments and dissimilarities bit-exact.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+EPS_GAP = 1e-5   # relative best/second-best gap below which a query is in the "gap set"
+RTOL = 1e-5      # float32 accumulation over 192 terms: 192 * 2^-24 ~ 1.1e-5
+
+
+@pytest.fixture(scope="module")
+def tb():
+    import tiler_b200
+    return tiler_b200
+
+
+def _check_search(oracle, ds, q, idx, err, k=1):
+    oi, od, nxt = oracle.knn_f64(ds, q, k)
+    o32i, o32d = oracle.knn_f32(ds, q, k)
+    idx = np.asarray(idx).reshape(len(q), k)
+    err = np.asarray(err).reshape(len(q), k)
+    # distances: every returned distance is the true distance of the returned row
+    true = np.array([[np.sum((q[i].astype(np.float64) - ds[idx[i, j]].astype(np.float64)) ** 2)
+                      for j in range(k)] for i in range(len(q))])
+    assert np.allclose(err, true, rtol=RTOL, atol=1e-7)
+    assert np.allclose(err, od, rtol=RTOL, atol=1e-7)
+    assert np.all(np.diff(err, axis=1) >= 0)
+    # indices: exact outside the gap set (gap judged on consecutive oracle distances)
+    allod = np.concatenate([od, nxt[:, None]], axis=1)
+    gap = np.diff(allod, axis=1) > EPS_GAP * np.maximum(allod[:, :-1], 1e-12)
+    prev_ok = np.concatenate([np.ones((len(q), 1), bool), gap[:, :-1]], axis=1)
+    solid = gap & prev_ok
+    assert np.array_equal(idx[solid], oi[solid])
+    return int((~solid).sum())
+
+
+def test_psyv_queries_bit_exact(tb, oracle, small_case):
+    for wavelets in (True, False):
+        for gamma in (-1, 0, 1):
+            got = tb.psyv_queries(small_case["rgb"][:300], wavelets=wavelets, gamma=gamma)
+            want = oracle.psyv_queries_f32(small_case["rgb"][:300], use_wavelets=wavelets, gamma=gamma)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), (wavelets, gamma)
+
+
+def test_psyv_edge_tiles(tb, oracle):
+    rgb = np.stack([np.zeros(64, np.int32), np.full(64, 0x00FFFFFF, np.int32),
+                    np.arange(64, dtype=np.int32) * 0x00040404, np.full(64, 0x7F0000FF, np.int32)])
+    got = tb.psyv_queries(rgb)
+    want = oracle.psyv_queries_f32(rgb)  # the top byte of $00BBGGRR is ignored (FromRGB main.pas:571)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert tb.psyv_queries(np.zeros((0, 64), np.int32)).shape == (0, 192)
+
+
+def test_tileset_dataset_bit_exact(tb, oracle, small_case):
+    for wavelets in (True, False):
+        with tb.KDTree.from_tileset(small_case["tiles"], small_case["pal"], wavelets=wavelets) as t:
+            assert (t.n, t.dd) == (512 * 4, 192)
+            want = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"], use_wavelets=wavelets)
+            assert np.array_equal(t.rows().view(np.uint32), want.view(np.uint32))
+
+
+def test_tileset_dataset_multi_palette_and_tile_flags(tb, oracle, small_case):
+    o = oracle
+    pals = np.stack([o.gen_palette(o.BASE_SEED + i)[0] for i in range(3)])
+    tiles = small_case["tiles"][:100]
+    flags = (np.arange(100) % 4).astype(np.uint8)
+    with tb.KDTree.from_tileset(tiles, pals, tile_flags=flags) as t:
+        got = t.rows().reshape(3, 100, 2, 2, 192)
+    for p in range(3):
+        for ti in (0, 1, 2, 3, 57):
+            for vm in (0, 1):
+                for hm in (0, 1):
+                    # hmir xor T^.HMirror, vmir xor T^.VMirror (main.pas:3912)
+                    want = o.psyv(palpix=tiles[ti], pal=pals[p], hmirror=hm ^ (flags[ti] & 1),
+                                  vmirror=vm ^ (flags[ti] >> 1)).astype(np.float32)
+                    assert np.array_equal(got[p, ti, vm, hm], want)
+
+
+def test_global_ft_rows(tb, oracle, small_case):
+    tree, tr_tile, tr_attrs = tb.KDTree.global_ft(small_case["tiles"])
+    want, wt, wa = oracle.global_rows_f32(small_case["tiles"])
+    assert np.array_equal(tree.rows(), want) and np.array_equal(tr_tile, wt) and np.array_equal(tr_attrs, wa)
+    # stage-1 search (UseOne main.pas:3830): k = 8 on palette-index rows, exact small integers
+    q = want[::37][:40]
+    idx, err = tree.search_batch(q, k=8)
+    oi, od, _ = oracle.knn_f64(want, q, 8)
+    assert np.array_equal(err, od.astype(np.float32))
+    assert np.array_equal(idx[:, 0] // 4, oi[:, 0] // 4) and np.all(err[:, 0] == 0)
+    tree.destroy()
+
+
+@pytest.mark.parametrize("engine", ["simt", "auto"])
+def test_search_batch_vs_oracle(tb, oracle, small_case, engine):
+    tb.set_engine(tb.ENGINE_SIMT if engine == "simt" else tb.ENGINE_AUTO)
+    try:
+        ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])
+        q = oracle.psyv_queries_f32(small_case["rgb"])
+        with tb.KDTree.from_rows(ds) as t:
+            idx, err = t.search_batch(q, k=1)
+            _check_search(oracle, ds, q, idx, err, 1)
+            o32i, o32d = oracle.knn_f32(ds, q, 1)
+            assert np.array_equal(err.view(np.uint32), o32d.view(np.uint32))  # same fp32 accumulation order
+            idx8, err8 = t.search_batch(q[:200], k=8)
+            _check_search(oracle, ds, q[:200], idx8, err8, 8)
+    finally:
+        tb.set_engine(tb.ENGINE_AUTO)
+
+
+def test_legacy_entry_points(tb, oracle, small_case):
+    ds = oracle.psyv_tileset_f32(small_case["tiles"][:64], small_case["pal"])
+    q = oracle.psyv_queries_f32(small_case["rgb"][:8])
+    t = tb.KDTree.create(ds)  # array-of-row-pointers path (extern.pas:63)
+    oi, od = oracle.knn_f32(ds, q, 8)
+    for i in range(8):
+        idx, err = t.search(q[i])
+        assert idx == oi[i, 0] and np.float32(err) == od[i, 0]
+        assert t.pri_search(q[i]) == (idx, err)
+        idxs, errs = t.search_multi(q[i], 8)
+        assert np.array_equal(idxs, oi[i]) and np.array_equal(errs, od[i])
+    t.destroy()
+    t.destroy()  # idempotent / NULL-safe
+
+
+def test_search_edge_cases(tb, oracle):
+    rng = np.random.default_rng(0)
+    # ragged sizes: n not a multiple of the tile, nq not a multiple of the block, dd not a multiple of 4
+    for n, nq, dd in [(1, 1, 192), (3, 5, 64), (65, 130, 192), (1000, 77, 50), (129, 64, 7)]:
+        ds = rng.standard_normal((n, dd)).astype(np.float32)
+        q = rng.standard_normal((nq, dd)).astype(np.float32)
+        k = min(n, 4)
+        with tb.KDTree.from_rows(ds) as t:
+            idx, err = t.search_batch(q, k=k)
+        oi, od = oracle.knn_f32(ds, q, k)
+        assert np.array_equal(idx, oi) and np.array_equal(err, od), (n, nq, dd)
+    # k > n: missing neighbours are index -1 / +inf
+    ds = rng.standard_normal((2, 16)).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        idx, err = t.search_batch(ds[:1], k=4)
+        assert list(idx[0, 2:]) == [-1, -1] and np.all(np.isinf(err[0, 2:]))
+        assert t.search_batch(np.zeros((0, 16), np.float32))[0].shape == (0, 1)
+    # exact duplicates: lowest index wins
+    ds = np.repeat(rng.standard_normal((1, 192)).astype(np.float32), 5, axis=0)
+    with tb.KDTree.from_rows(ds) as t:
+        idx, err = t.search_batch(ds[:1], k=3)
+        assert list(idx[0]) == [0, 1, 2] and np.all(err == 0)
+    # empty dataset
+    with tb.KDTree.from_rows(np.zeros((0, 192), np.float32)) as t:
+        idx, err = t.search_batch(np.zeros((3, 192), np.float32))
+        assert np.all(idx == -1)
+
+
+def test_frametiling_fused(tb, oracle, small_case):
+    ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])
+    q = oracle.psyv_queries_f32(small_case["rgb"])
+    with tb.KDTree.from_tileset(small_case["tiles"], small_case["pal"]) as t:
+        idx, err = t.frametiling_search(small_case["rgb"])
+    ingap = _check_search(oracle, ds, q, idx, err, 1)
+    assert ingap < 0.01 * len(q)
+    # row -> (tile, attrs) mapping of DoPsyV (main.pas:3908-3910): planted queries come back
+    # as their tile with err << 1 (noise only)
+    assert np.median(err) < 0.1
+
+
+def test_kmodes_assign_bit_exact(tb, oracle, small_case):
+    o = oracle
+    tiles, _ = o.gen_tileset(o.BASE_SEED + 9, 6000)
+    X = o.kmodes_rows(tiles)
+    cent = X[::23][:200].copy()
+    for sem in (tb.KM_ASM, tb.KM_GENERIC):
+        clust, dis = tb.kmodes_assign(X, cent, sem)
+        wc, wd = o.kmodes_assign(X, cent, sem)
+        assert np.array_equal(clust, wc) and np.array_equal(dis, wd), sem
+    # arbitrary bytes (wrap-around of pabsb/psubb), duplicate centroids (last index wins), k not a tile multiple
+    rng = np.random.default_rng(4)
+    X = rng.integers(0, 256, (777, 80)).astype(np.uint8)
+    cent = rng.integers(0, 256, (513, 80)).astype(np.uint8)
+    cent[500] = cent[3]
+    X[5] = cent[3]
+    for sem in (tb.KM_ASM, tb.KM_GENERIC):
+        clust, dis = tb.kmodes_assign(X, cent, sem)
+        wc, wd = o.kmodes_assign(X, cent, sem)
+        assert np.array_equal(clust, wc) and np.array_equal(dis, wd), sem
+        assert clust[5] == 500 and dis[5] == 0
+    # single centroid, empty inputs
+    clust, dis = tb.kmodes_assign(X[:10], cent[:1])
+    assert np.all(clust == 0)
+    assert tb.kmodes_assign(X[:0], cent)[0].shape == (0,)
+    clust, dis = tb.kmodes_assign(X[:4], cent[:0])
+    assert np.all(clust == -1) and np.all(dis == np.uint64(2 ** 64 - 1))
+
+
+def test_kmodes_update_min_distance(tb, oracle):
+    rng = np.random.default_rng(6)
+    X = rng.integers(0, 16, (5000, 80)).astype(np.uint8)
+    md = rng.integers(0, 60000, 5000).astype(np.uint64)
+    md[::3] = np.uint64(2 ** 64 - 1)
+    for sem in (tb.KM_ASM, tb.KM_GENERIC):
+        got = tb.kmodes_update_min_distance(X, X[17], md, sem)
+        assert np.array_equal(got, oracle.update_min_distance(X, X[17], md, sem))
+
+
+def test_device_pointer_entry_points(tb, oracle, small_case):
+    import torch
+    ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])
+    q = oracle.psyv_queries_f32(small_case["rgb"])
+    d_rgb = torch.from_numpy(small_case["rgb"]).cuda()
+    d_idx = torch.empty(len(q), dtype=torch.int32, device="cuda")
+    d_err = torch.empty(len(q), dtype=torch.float32, device="cuda")
+    t = tb.KDTree.from_tileset(torch.from_numpy(small_case["tiles"]).cuda(),
+                               torch.from_numpy(small_case["pal"]).cuda().reshape(1, -1))
+    t.frametiling_search(d_rgb, out_idx=d_idx, out_err=d_err)
+    torch.cuda.synchronize()
+    _check_search(oracle, ds, q, d_idx.cpu().numpy(), d_err.cpu().numpy(), 1)
+    d_desc = torch.empty((len(q), 192), dtype=torch.float32, device="cuda")
+    tb.psyv_queries(d_rgb, out=d_desc)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_desc.cpu().numpy(), q)
+    st = tb.stats()
+    assert st["kernel_launches"] > 0 and st["queries"] >= len(q)
+    t.destroy()

@@ -1,0 +1,10 @@
+"""tiler_b200 — B200-native FrameTiling best-tile search + KModes assignment.
+
+The product is tiler_b200/libtmann.so (hand-written sm_100a CUDA behind the
+reference's ANN.dll C ABI, include/tmann.h).  This package is the thin host
+mirror used by tests and bench.py.  Importing it requires the built library.
+"""
+from . import ann  # noqa: F401
+from .ann import (ENGINE_AUTO, ENGINE_SIMT, ENGINE_TC, KM_ASM, KM_GENERIC, KDTree,  # noqa: F401
+                  kmodes_assign, kmodes_update_min_distance, psyv_queries, reset_stats,
+                  set_device, set_engine, set_profiling, set_stream, stats)

@@ -1,0 +1,212 @@
+"""Python view of the C ABI (include/tmann.h), named after the reference's bindings
+(extern.pas:63-67) so parity tests read like calls the encoder makes.
+
+numpy arrays are HOST buffers (the h_* entry points, copies inside the call);
+objects with a ``data_ptr()`` (torch CUDA tensors) are DEVICE buffers (the d_*
+entry points).  torch is never imported here: it is plumbing of the callers.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import TMStats, check, check_handle, lib
+
+PSYV_WAVELETS, PSYV_QWEIGHT = 1, 2
+KM_ASM, KM_GENERIC = 0, 1
+ENGINE_AUTO, ENGINE_SIMT, ENGINE_TC = 0, 1, 2
+
+
+def _hp(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _is_dev(x):
+    return hasattr(x, "data_ptr")
+
+
+def _dp(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def set_device(dev):
+    check(lib.tm_set_device(int(dev)))
+
+
+def set_engine(engine):
+    check(lib.tm_set_engine(int(engine)))
+
+
+def set_stream(cuda_stream_ptr):
+    check(lib.tm_set_stream(C.c_void_p(int(cuda_stream_ptr))))
+
+
+def stats():
+    s = TMStats()
+    check(lib.tm_get_stats(C.byref(s)))
+    return {f: getattr(s, f) for f, _ in TMStats._fields_}
+
+
+def set_profiling(on):
+    check(lib.tm_set_profiling(int(bool(on))))
+
+
+def reset_stats():
+    check(lib.tm_reset_stats())
+
+
+class KDTree:
+    """Dataset handle (PANNkdtree, extern.pas:36-39)."""
+
+    def __init__(self, handle, attrs=None):
+        self._h = None
+        self._h = check_handle(handle)
+        self.attrs = attrs or {}
+
+    # -- constructors ---------------------------------------------------------
+    @classmethod
+    def create(cls, rows):
+        """ann_kdtree_create through an array of row pointers (extern.pas:63)."""
+        rows = np.ascontiguousarray(rows, np.float32)
+        n, dd = rows.shape
+        ptrs = (C.c_void_p * max(n, 1))(*[rows[i].ctypes.data for i in range(n)])
+        return cls(lib.ann_kdtree_create(ptrs, n, dd, 1, 0))
+
+    @classmethod
+    def from_rows(cls, rows):
+        if _is_dev(rows):
+            n, dd = rows.shape
+            return cls(lib.tm_dataset_create(_dp(rows), n, dd, 1))
+        rows = np.ascontiguousarray(rows, np.float32)
+        return cls(lib.tm_dataset_create(_hp(rows), rows.shape[0], rows.shape[1], 0))
+
+    @classmethod
+    def from_tileset(cls, palpix, pals, tile_flags=None, wavelets=True, gamma=-1, qweight=False):
+        """Stage-2 dataset of DoPsyV (main.pas:3883-3919), all (pal, tile, vmir, hmir) used."""
+        flags = (PSYV_WAVELETS if wavelets else 0) | (PSYV_QWEIGHT if qweight else 0)
+        if _is_dev(palpix):
+            npal, ps = pals.shape
+            h = lib.tm_tileset_dataset_create_dev(_dp(palpix), palpix.shape[0], _dp(pals), npal, ps,
+                                                  _dp(tile_flags), flags, gamma)
+            return cls(h)
+        palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+        pals = np.ascontiguousarray(pals, np.int32)
+        pals = pals.reshape(1, -1) if pals.ndim == 1 else pals
+        tf = None if tile_flags is None else np.ascontiguousarray(tile_flags, np.uint8)
+        h = lib.tm_tileset_dataset_create(_hp(palpix), palpix.shape[0], _hp(pals), pals.shape[0],
+                                          pals.shape[1], _hp(tf), flags, gamma)
+        return cls(h)
+
+    @classmethod
+    def global_ft(cls, palpix):
+        """PrepareGlobalFT (main.pas:3736-3780): returns (tree, TRToTileIdx, TRToAttrs)."""
+        palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+        n = palpix.shape[0] * 4
+        tr_tile = np.empty(n, np.int32)
+        tr_attrs = np.empty(n, np.uint8)
+        h = lib.tm_global_dataset_create(_hp(palpix), palpix.shape[0], _hp(tr_tile), _hp(tr_attrs))
+        return cls(h), tr_tile, tr_attrs
+
+    # -- lifetime ---------------------------------------------------------------
+    def destroy(self):
+        if self._h:
+            lib.ann_kdtree_destroy(self._h)
+            self._h = None
+
+    __del__ = destroy
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.destroy()
+
+    @property
+    def n(self):
+        return int(lib.tm_dataset_rows(self._h))
+
+    @property
+    def dd(self):
+        return int(lib.tm_dataset_dim(self._h))
+
+    def rows(self):
+        out = np.empty((self.n, self.dd), np.float32)
+        check(lib.tm_dataset_read(self._h, _hp(out)))
+        return out
+
+    # -- legacy single-query entry points (extern.pas:65-67) ----------------------
+    def search(self, q, eps=0.0):
+        q = np.ascontiguousarray(q, np.float32)
+        err = C.c_float()
+        idx = lib.ann_kdtree_search(self._h, _hp(q), eps, C.byref(err))
+        return idx, err.value
+
+    def pri_search(self, q, eps=0.0):
+        q = np.ascontiguousarray(q, np.float32)
+        err = C.c_float()
+        idx = lib.ann_kdtree_pri_search(self._h, _hp(q), eps, C.byref(err))
+        return idx, err.value
+
+    def search_multi(self, q, cnt, eps=0.0):
+        q = np.ascontiguousarray(q, np.float32)
+        idxs = np.full(cnt, -1, np.int32)
+        errs = np.zeros(cnt, np.float32)
+        lib.ann_kdtree_search_multi(self._h, _hp(idxs), _hp(errs), cnt, _hp(q), eps)
+        return idxs, errs
+
+    # -- batch ------------------------------------------------------------------
+    def search_batch(self, q, k=1, out_idx=None, out_err=None):
+        if _is_dev(q):
+            check(lib.tm_search_batch_dev(self._h, _dp(q), q.shape[0], k, _dp(out_idx), _dp(out_err)))
+            return out_idx, out_err
+        q = np.ascontiguousarray(q, np.float32).reshape(-1, self.dd)
+        idx = np.empty((q.shape[0], k), np.int32)
+        err = np.empty((q.shape[0], k), np.float32)
+        check(lib.ann_kdtree_search_batch(self._h, _hp(q), q.shape[0], k, _hp(idx), _hp(err)))
+        return idx, err
+
+    def frametiling_search(self, rgb, wavelets=True, gamma=-1, out_idx=None, out_err=None):
+        """DoFrameTiling hot loop (main.pas:4020-4038) for a batch of RGB tiles."""
+        flags = PSYV_WAVELETS if wavelets else 0
+        if _is_dev(rgb):
+            check(lib.tm_frametiling_search_dev(self._h, _dp(rgb), rgb.shape[0], flags, gamma,
+                                                _dp(out_idx), _dp(out_err)))
+            return out_idx, out_err
+        rgb = np.ascontiguousarray(rgb, np.int32).reshape(-1, 64)
+        idx = out_idx if out_idx is not None else np.empty(rgb.shape[0], np.int32)
+        err = out_err if out_err is not None else np.empty(rgb.shape[0], np.float32)
+        check(lib.tm_frametiling_search(self._h, _hp(rgb), rgb.shape[0], flags, gamma, _hp(idx), _hp(err)))
+        return idx, err
+
+
+def psyv_queries(rgb, wavelets=True, gamma=-1, qweight=False, out=None):
+    flags = (PSYV_WAVELETS if wavelets else 0) | (PSYV_QWEIGHT if qweight else 0)
+    if _is_dev(rgb):
+        check(lib.tm_psyv_queries_dev(_dp(rgb), rgb.shape[0], flags, gamma, _dp(out)))
+        return out
+    rgb = np.ascontiguousarray(rgb, np.int32).reshape(-1, 64)
+    out = np.empty((rgb.shape[0], 192), np.float32)
+    check(lib.tm_psyv_queries(_hp(rgb), rgb.shape[0], flags, gamma, _hp(out)))
+    return out
+
+
+def kmodes_assign(X, centroids, semantics=KM_ASM, out_clust=None, out_dis=None):
+    """TKModes.DoGMMD over all points (kmodes.pas:825-835, 984-997)."""
+    if _is_dev(X):
+        check(lib.tm_kmodes_assign_dev(_dp(X), X.shape[0], _dp(centroids), centroids.shape[0], semantics,
+                                       _dp(out_clust), _dp(out_dis)))
+        return out_clust, out_dis
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    centroids = np.ascontiguousarray(centroids, np.uint8).reshape(-1, 80)
+    clust = np.empty(X.shape[0], np.int32)
+    dis = np.empty(X.shape[0], np.uint64)
+    check(lib.tm_kmodes_assign(_hp(X), X.shape[0], _hp(centroids), centroids.shape[0], semantics,
+                               _hp(clust), _hp(dis)))
+    return clust, dis
+
+
+def kmodes_update_min_distance(X, center, mindist, semantics=KM_ASM):
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    center = np.ascontiguousarray(center, np.uint8)
+    mindist = np.ascontiguousarray(mindist, np.uint64).copy()
+    check(lib.tm_kmodes_update_min_distance(_hp(X), X.shape[0], _hp(center), semantics, _hp(mindist)))
+    return mindist

@@ -1,0 +1,323 @@
+// psyv.cu — descriptor pack/mirror kernels (sm_100a).
+//
+// Replaces ComputeTilePsyVisFeatures (reference main.pas:2997-3177) for the two
+// producers on the FrameTiling path: query tiles from true-colour pixels
+// (main.pas:4023) and tileset rows rendered from a palette in the four H/V
+// orientations (DoPsyV main.pas:3883-3919), plus the stage-1 palette-index rows
+// of PrepareGlobalFT (main.pas:3736-3780).
+//
+// The arithmetic is FP64 in the reference's operation order, compiled with
+// -fmad=false, so the float32 rows written here are bit-identical to what the
+// Pascal code hands to ANN.  One thread owns one (tile, colour plane): 64 doubles
+// in registers, the 3-level Haar (WaveletGS main.pas:2805-2840) fully unrolled.
+// HBM-bound by design: 256 B in, 768 B out per query tile.
+#include "tm_common.cuh"
+#include <math.h>
+
+namespace {
+
+struct PsyvTables {      // host-built, mirrors InitLuts main.pas:592-623
+    double f[256];       // gGammaCorLut[g][c] (c/255 or pow)
+    double fr[256];      // cRedMul * f
+    double fg[256];      // cGreenMul * f
+    double fb[256];      // cBlueMul * f
+};
+
+struct PsyvConsts {
+    double cu, cv, luma_div, haar;
+};
+
+__device__ double *g_dct_lut_dev = nullptr; // unused placeholder (lut passed by pointer)
+
+// One Haar level on the top-left N x N of an 8 x 8 (stride 8) block; same
+// operation order as WaveletGS: rows first into tx, then columns.
+template <int N>
+__device__ __forceinline__ void haar_level(double (&a)[64], double f) {
+    // in place, one row (then one column) of temporaries at a time: 64 + N live doubles
+#pragma unroll
+    for (int y = 0; y < N; y++) {
+        double t[N];
+#pragma unroll
+        for (int x = 0; x < N / 2; x++) {
+            double p = a[y * 8 + 2 * x], q = a[y * 8 + 2 * x + 1];
+            t[x] = (p + q) * f;
+            t[x + N / 2] = (p - q) * f;
+        }
+#pragma unroll
+        for (int x = 0; x < N; x++) a[y * 8 + x] = t[x];
+    }
+#pragma unroll
+    for (int x = 0; x < N; x++) {
+        double t[N];
+#pragma unroll
+        for (int y = 0; y < N / 2; y++) {
+            double p = a[(2 * y) * 8 + x], q = a[(2 * y + 1) * 8 + x];
+            t[y] = (p + q) * f;
+            t[y + N / 2] = (p - q) * f;
+        }
+#pragma unroll
+        for (int y = 0; y < N; y++) a[y * 8 + x] = t[y];
+    }
+}
+
+__device__ __forceinline__ double plane_value(int32_t col, int plane, const PsyvTables *T,
+                                              const PsyvConsts &K) {
+    int r = col & 0xff, g = (col >> 8) & 0xff, b = (col >> 16) & 0xff; // FromRGB main.pas:571-576
+    double y = ((T->fr[r] + T->fg[g]) + T->fb[b]) / K.luma_div;         // main.pas:2674
+    if (plane == 0) return y;
+    if (plane == 1) return (T->f[b] - y) * K.cu;                         // main.pas:2675
+    return (T->f[r] - y) * K.cv;                                         // main.pas:2676
+}
+
+__device__ __forceinline__ void store_row_f32(float *dst, const double (&a)[64]) {
+    float4 *d4 = reinterpret_cast<float4 *>(dst);
+#pragma unroll
+    for (int i = 0; i < 16; i++)
+        d4[i] = make_float4((float)a[4 * i], (float)a[4 * i + 1], (float)a[4 * i + 2], (float)a[4 * i + 3]);
+}
+
+// DCT-II branch main.pas:3075-3174: z = sum_{y,x} cpn*lut (sequential), optional Q weight, * cUVRatio
+__device__ __forceinline__ void dct_plane(const double (&a)[64], const double *lut, const double *qw,
+                                          int plane, float *dst) {
+    for (int vu = 0; vu < 64; vu++) {
+        const double *l = lut + vu * 64;
+        double z = 0.0;
+#pragma unroll
+        for (int i = 0; i < 64; i++) z += a[i] * l[i];
+        if (qw) z *= qw[plane * 64 + vu];
+        dst[vu] = (float)(z * lut[4096 + vu]);
+    }
+}
+
+template <bool WAVELETS>
+__global__ void __launch_bounds__(192) psyv_queries_kernel(const int32_t *__restrict__ rgb, int64_t nq,
+                                                            const PsyvTables *__restrict__ tabs,
+                                                            PsyvConsts K, const double *__restrict__ lut,
+                                                            const double *__restrict__ qw,
+                                                            float *__restrict__ out) {
+    __shared__ PsyvTables T;
+    for (int i = threadIdx.x; i < (int)(sizeof(PsyvTables) / 8); i += blockDim.x)
+        reinterpret_cast<double *>(&T)[i] = reinterpret_cast<const double *>(tabs)[i];
+    __syncthreads();
+    // 64 tiles per block; lanes of a warp take consecutive tiles of ONE plane so the
+    // plane branch is warp-uniform (192 threads = 3 planes x 64 tiles).
+    int plane = threadIdx.x / 64;
+    int64_t q = (int64_t)blockIdx.x * 64 + (threadIdx.x & 63);
+    if (q >= nq) return;
+    const int4 *src = reinterpret_cast<const int4 *>(rgb + q * 64);
+    double a[64];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        int4 v = __ldg(src + i);
+        a[4 * i + 0] = plane_value(v.x, plane, &T, K);
+        a[4 * i + 1] = plane_value(v.y, plane, &T, K);
+        a[4 * i + 2] = plane_value(v.z, plane, &T, K);
+        a[4 * i + 3] = plane_value(v.w, plane, &T, K);
+    }
+    float *dst = out + q * TM_DCT + plane * 64;
+    if (WAVELETS) {
+        haar_level<8>(a, K.haar);
+        haar_level<4>(a, K.haar);
+        haar_level<2>(a, K.haar);
+        store_row_f32(dst, a);
+    } else {
+        dct_plane(a, lut, qw, plane, dst);
+    }
+}
+
+// tileset rows: thread = (row, plane); row r = ((p*ntiles + t)*2 + vmir)*2 + hmir
+template <bool WAVELETS>
+__global__ void __launch_bounds__(192) psyv_tileset_kernel(const uint8_t *__restrict__ palpix, int64_t ntiles,
+                                                            const int32_t *__restrict__ pals, int npal,
+                                                            int pal_size, const uint8_t *__restrict__ tflags,
+                                                            const PsyvTables *__restrict__ tabs, PsyvConsts K,
+                                                            const double *__restrict__ lut,
+                                                            const double *__restrict__ qw,
+                                                            float *__restrict__ out) {
+    __shared__ PsyvTables T;
+    for (int i = threadIdx.x; i < (int)(sizeof(PsyvTables) / 8); i += blockDim.x)
+        reinterpret_cast<double *>(&T)[i] = reinterpret_cast<const double *>(tabs)[i];
+    __syncthreads();
+    int plane = threadIdx.x / 64;
+    int64_t row = (int64_t)blockIdx.x * 64 + (threadIdx.x & 63);
+    int64_t nrows = ntiles * 4 * npal;
+    if (row >= nrows) return;
+    int hmir = (int)(row & 1), vmir = (int)((row >> 1) & 1);
+    int64_t t = (row >> 2) % ntiles;
+    int p = (int)((row >> 2) / ntiles);
+    int fl = tflags ? tflags[t] : 0;
+    hmir ^= (fl & 1);          // hmir xor T^.HMirror main.pas:3912
+    vmir ^= ((fl >> 1) & 1);
+    const int32_t *pal = pals + (int64_t)p * pal_size;
+    // 64 palette indices as 4 x uint4
+    const uint4 *src = reinterpret_cast<const uint4 *>(palpix + t * 64);
+    uint32_t w[16];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        uint4 v = __ldg(src + i);
+        w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+    }
+    double a[64];
+#pragma unroll
+    for (int y = 0; y < 8; y++)
+#pragma unroll
+        for (int x = 0; x < 8; x++) {
+            // output pixel (x,y) takes source pixel (xx,yy) main.pas:3041-3046
+            int word_n = y * 2 + (x >> 2), word_v = (7 - y) * 2 + (x >> 2);
+            int word_hn = y * 2 + ((7 - x) >> 2), word_hv = (7 - y) * 2 + ((7 - x) >> 2);
+            uint32_t wn = vmir ? (hmir ? w[word_hv] : w[word_v]) : (hmir ? w[word_hn] : w[word_n]);
+            int sh = hmir ? ((7 - x) & 3) * 8 : (x & 3) * 8;
+            int pi = (wn >> sh) & 0xff;
+            a[y * 8 + x] = plane_value(__ldg(pal + pi), plane, &T, K);
+        }
+    float *dst = out + row * TM_DCT + plane * 64;
+    if (WAVELETS) {
+        haar_level<8>(a, K.haar);
+        haar_level<4>(a, K.haar);
+        haar_level<2>(a, K.haar);
+        store_row_f32(dst, a);
+    } else {
+        dct_plane(a, lut, qw, plane, dst);
+    }
+}
+
+// stage-1 rows (PrepareGlobalFT main.pas:3736-3780): order (none, H, H+V, V)
+__global__ void global_rows_kernel(const uint8_t *__restrict__ palpix, int64_t ntiles,
+                                   float *__restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; // one thread per output float4
+    int64_t total = ntiles * 4 * 16;
+    if (i >= total) return;
+    int c4 = (int)(i & 15);
+    int o = (int)((i >> 4) & 3);
+    int64_t t = i >> 6;
+    int hm = (o == 1 || o == 2), vm = (o >= 2);
+    int y = c4 >> 1, x0 = (c4 & 1) * 4;
+    int sy = vm ? 7 - y : y;
+    const uint8_t *src = palpix + t * 64 + sy * 8;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        int x = x0 + j;
+        v[j] = (float)src[hm ? 7 - x : x];
+    }
+    reinterpret_cast<float4 *>(out)[i] = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+struct PsyvDeviceState {
+    PsyvTables *tabs[3] = {nullptr, nullptr, nullptr}; // gamma -1, 0, 1
+    double *lut = nullptr;                            // 4096 DCT lut + 64 cUVRatio
+    double *qw = nullptr;                             // 192 Q weights
+    int device = -1;
+    std::mutex mu;
+} g_ps;
+
+const int q_luma[64] = {16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55,
+                        14, 13, 16, 24, 40, 57, 69, 56, 14, 17, 22, 29, 51, 87, 80, 62,
+                        18, 22, 37, 56, 68, 109, 103, 77, 24, 35, 55, 64, 81, 104, 113, 92,
+                        49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99};
+const int q_chroma[64] = {17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99, 99, 112,
+                          24, 26, 56, 99, 99, 99, 112, 128, 47, 66, 99, 99, 99, 112, 128, 144,
+                          99, 99, 99, 99, 112, 128, 144, 160, 99, 99, 99, 112, 128, 144, 160, 176,
+                          99, 99, 112, 128, 144, 160, 176, 192, 99, 112, 128, 144, 160, 176, 192, 208};
+
+int ensure_tables() {
+    std::lock_guard<std::mutex> lk(g_ps.mu);
+    int dev;
+    TM_CUDA(cudaGetDevice(&dev));
+    if (g_ps.device == dev && g_ps.lut) return 0;
+    static const double gam[2] = {2.0, 0.6}; // main.pas:586
+    for (int g = -1; g < 2; g++) {
+        PsyvTables *h = new PsyvTables;
+        for (int c = 0; c < 256; c++) {
+            double f = g >= 0 ? pow(c / 255.0, gam[g]) : c / 255.0; // main.pas:596-601
+            h->f[c] = f;
+            h->fr[c] = 2126.0 * f;
+            h->fg[c] = 7152.0 * f;
+            h->fb[c] = 722.0 * f;
+        }
+        TM_CUDA(cudaMalloc(&g_ps.tabs[g + 1], sizeof(PsyvTables)));
+        TM_CUDA(cudaMemcpy(g_ps.tabs[g + 1], h, sizeof(PsyvTables), cudaMemcpyHostToDevice));
+        delete h;
+    }
+    double *lut = new double[4096 + 64];
+    int i = 0;
+    for (int v = 0; v < 8; v++)
+        for (int u = 0; u < 8; u++)
+            for (int y = 0; y < 8; y++)
+                for (int x = 0; x < 8; x++)
+                    lut[i++] = cos((x + 0.5) * u * M_PI / 16.0) * cos((y + 0.5) * v * M_PI / 16.0);
+    for (int v = 0; v < 8; v++)
+        for (int u = 0; u < 8; u++) {
+            double r = (u == 0 ? sqrt(0.5) : 1.0) * (v == 0 ? sqrt(0.5) : 1.0);
+            if (u == 0 && v == 0) r = 0.5;
+            lut[4096 + v * 8 + u] = r;
+        }
+    TM_CUDA(cudaMalloc(&g_ps.lut, sizeof(double) * (4096 + 64)));
+    TM_CUDA(cudaMemcpy(g_ps.lut, lut, sizeof(double) * (4096 + 64), cudaMemcpyHostToDevice));
+    delete[] lut;
+    double qw[192];
+    for (int c = 0; c < 3; c++)
+        for (int j = 0; j < 64; j++) qw[c * 64 + j] = sqrt(16.0) / sqrt((double)(c == 0 ? q_luma : q_chroma)[j]);
+    TM_CUDA(cudaMalloc(&g_ps.qw, sizeof(qw)));
+    TM_CUDA(cudaMemcpy(g_ps.qw, qw, sizeof(qw), cudaMemcpyHostToDevice));
+    g_ps.device = dev;
+    return 0;
+}
+
+PsyvConsts make_consts() {
+    PsyvConsts K;
+    const double luma = 2126.0 + 7152.0 + 722.0;
+    K.cu = 0.5 / (1.0 - 722.0 / luma);
+    K.cv = 0.5 / (1.0 - 2126.0 / luma);
+    K.luma_div = luma;
+    K.haar = 1.0 / sqrt(2.0);
+    return K;
+}
+
+} // namespace
+
+int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
+                           cudaStream_t s) {
+    if (gamma < -1 || gamma > 1) { tm_set_error("gamma must be -1, 0 or 1"); return TM_EINVAL; }
+    if (nq == 0) return 0;
+    int r = ensure_tables();
+    if (r) return r;
+    PsyvConsts K = make_consts();
+    unsigned grid = (unsigned)((nq + 63) / 64);
+    const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
+    if (flags & TM_PSYV_WAVELETS)
+        psyv_queries_kernel<true><<<grid, 192, 0, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+    else
+        psyv_queries_kernel<false><<<grid, 192, 0, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "psyv_queries_kernel");
+}
+
+int tm_launch_psyv_tileset(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal,
+                           int pal_size, const uint8_t *d_tile_flags, int flags, int gamma,
+                           float *d_out, cudaStream_t s) {
+    if (gamma < -1 || gamma > 1) { tm_set_error("gamma must be -1, 0 or 1"); return TM_EINVAL; }
+    int64_t nrows = ntiles * 4 * npal;
+    if (nrows == 0) return 0;
+    int r = ensure_tables();
+    if (r) return r;
+    PsyvConsts K = make_consts();
+    unsigned grid = (unsigned)((nrows + 63) / 64);
+    const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
+    if (flags & TM_PSYV_WAVELETS)
+        psyv_tileset_kernel<true><<<grid, 192, 0, s>>>(d_palpix, ntiles, d_pals, npal, pal_size, d_tile_flags,
+                                                       g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+    else
+        psyv_tileset_kernel<false><<<grid, 192, 0, s>>>(d_palpix, ntiles, d_pals, npal, pal_size, d_tile_flags,
+                                                        g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "psyv_tileset_kernel");
+}
+
+int tm_launch_global_rows(const uint8_t *d_palpix, int64_t ntiles, float *d_out, cudaStream_t s) {
+    int64_t total = ntiles * 64;
+    if (total == 0) return 0;
+    global_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_palpix, ntiles, d_out);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "global_rows_kernel");
+}

@@ -1,0 +1,87 @@
+// tm_common.cuh — shared declarations of libtmann.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <atomic>
+#include <mutex>
+#include "../../include/tmann.h"
+
+#define TM_DCT 192
+#define TM_KM_FEATURES 80
+
+// Dataset handle behind the opaque ANNkdtree*.  Layout in HBM:
+//   rows_f32 [n][dd]      float32, exact copy of what crossed the FFI (re-rank / SIMT path)
+//   rows_f16 [n_pad][kp]  fp16 operand of the tensor-core pass: mean-centred row, then the
+//                         fp32 ||t-mu||^2 split in three fp16 parts, zero padded to kp
+//   norms    [n]          float32 ||t-mu||^2 (fp32 from the unrounded centred row)
+//   mean     [dd]         float32 column mean (distance-invariant centring)
+struct ANNkdtree {
+    uint32_t magic;
+    int64_t n;
+    int dd;
+    int device;
+    float *rows_f32;
+    __half *rows_f16;
+    float *norms;
+    float *mean;
+    int64_t n_pad;
+    int kp;
+    float max_norm;  // max ||t-mu||
+    void *tmap_rows; // CUtensorMap (host copy) for rows_f16
+    std::mutex *single_mu; // serialises the legacy one-query entry points' scratch
+    float *h_pin;          // pinned scratch for the legacy one-query entry points
+    float *d_q1;
+    int *d_i1;
+    float *d_e1;
+};
+#define TM_MAGIC 0x544d414eu
+
+void tm_set_error(const char *fmt, ...);
+int tm_check(cudaError_t e, const char *what);
+#define TM_CUDA(x)                                  \
+    do {                                            \
+        int _r = tm_check((x), #x);                 \
+        if (_r) return _r;                          \
+    } while (0)
+
+extern std::atomic<int64_t> g_launches, g_queries, g_fallbacks;
+extern int g_engine;
+static inline void tm_count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+int tm_ensure_device();
+int tm_prof_begin(int tag, cudaStream_t s); // returns a token (-1 when profiling is off)
+void tm_prof_end(int token, cudaStream_t s);
+cudaStream_t tm_stream();
+int tm_num_sms();
+
+// ---- descriptor kernels (psyv.cu)
+int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
+                           cudaStream_t s);
+int tm_launch_psyv_tileset(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal,
+                           int pal_size, const uint8_t *d_tile_flags, int flags, int gamma,
+                           float *d_out, cudaStream_t s);
+int tm_launch_global_rows(const uint8_t *d_palpix, int64_t ntiles, float *d_out, cudaStream_t s);
+
+// ---- dataset preparation (prep.cu): mean, centred fp16 operand, norms
+int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s);
+// query operand: centred fp16 rows + [1,1,1] tail, fp32 ||q-mu||^2
+int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, __half *d_q16,
+                            float *d_qnorm, cudaStream_t s);
+
+// ---- exact SIMT search (search_simt.cu): sequential fp32 accumulation, lowest index on ties
+int tm_launch_search_simt(const float *d_rows, int64_t n, int dd, const float *d_q, int64_t nq, int k,
+                          int *d_idx, float *d_err, cudaStream_t s);
+// exact search restricted to a list of query ids (fallback path)
+int tm_launch_search_simt_list(const float *d_rows, int64_t n, int dd, const float *d_q,
+                               const int *d_qlist, const int *d_qcount, int64_t max_list, int k,
+                               int *d_idx, float *d_err, cudaStream_t s);
+// ---- tensor-core search (search_tc.cu)
+int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err,
+                 cudaStream_t s);
+// ---- kmodes (kmodes.cu)
+int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
+                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s);
+int tm_launch_kmodes_umd(const uint8_t *d_X, int64_t np, const uint8_t *d_center, int sem,
+                         uint64_t *d_mind, cudaStream_t s);
