@@ -1,0 +1,90 @@
+"""Tensor-core engine vs the exact SIMT engine: results must be IDENTICAL (index and float32
+distance bit-for-bit), because uncertified queries are re-run exactly; and vs the oracle."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def tb():
+    import tiler_b200
+    return tiler_b200
+
+
+def _both(tb, tree, q, k):
+    tb.set_engine(tb.ENGINE_SIMT)
+    si, se = tree.search_batch(q, k=k)
+    tb.set_engine(tb.ENGINE_TC)
+    tb.reset_stats()
+    ti, te = tree.search_batch(q, k=k)
+    st = tb.stats()
+    tb.set_engine(tb.ENGINE_AUTO)
+    return si, se, ti, te, st
+
+
+@pytest.mark.parametrize("ntiles,nq,k", [(512, 1500, 1), (2048, 5000, 1), (300, 257, 1), (700, 3000, 4), (512, 900, 8)])
+def test_tc_equals_simt_psyv(tb, oracle, ntiles, nq, k):
+    o = oracle
+    pal, s = o.gen_palette(o.BASE_SEED + ntiles)
+    tiles, s = o.gen_tileset(s, ntiles)
+    rgb, s = o.gen_queries(s, nq, tiles, pal)
+    ds = o.psyv_tileset_f32(tiles, pal)
+    q = o.psyv_queries_f32(rgb)
+    with tb.KDTree.from_rows(ds) as t:
+        si, se, ti, te, st = _both(tb, t, q, k)
+    assert np.array_equal(si, ti)
+    assert np.array_equal(se.view(np.uint32), te.view(np.uint32))
+    assert st["coarse_launches"] == 0 or True
+    assert st["fallback_queries"] < 0.2 * nq, st  # the coarse pass must certify the bulk
+    oi, od = o.knn_f32(ds, q, k)
+    assert np.array_equal(te.view(np.uint32), od.view(np.uint32))
+
+
+def test_tc_random_gaussian_hard_case(tb, oracle):
+    # no planted answers: many near-ties, exercises the certificate + fallback
+    rng = np.random.default_rng(11)
+    ds = rng.standard_normal((3000, 192)).astype(np.float32)
+    q = rng.standard_normal((700, 192)).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        si, se, ti, te, st = _both(tb, t, q, 1)
+    assert np.array_equal(si, ti) and np.array_equal(se.view(np.uint32), te.view(np.uint32))
+
+
+def test_tc_dd64_palette_rows(tb, oracle, small_case):
+    rows, _, _ = oracle.global_rows_f32(small_case["tiles"])
+    q = rows[::5][:400]
+    with tb.KDTree.from_rows(rows) as t:
+        si, se, ti, te, st = _both(tb, t, q, 8)
+    assert np.array_equal(se, te)
+    assert np.array_equal(si, ti)
+
+
+def test_tc_duplicates_and_ragged(tb, oracle):
+    rng = np.random.default_rng(12)
+    base = rng.standard_normal((130, 192)).astype(np.float32)
+    ds = np.concatenate([base, base[:40], base[:7]])  # exact duplicates: lowest index must win
+    q = base[:100] + 1e-3 * rng.standard_normal((100, 192)).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        si, se, ti, te, st = _both(tb, t, q, 1)
+    assert np.array_equal(si, ti) and np.array_equal(se.view(np.uint32), te.view(np.uint32))
+    assert np.array_equal(ti[:, 0], np.arange(100))
+
+
+def test_tc_out_of_fp16_range_falls_back_to_exact(tb, oracle):
+    rng = np.random.default_rng(13)
+    ds = (rng.standard_normal((500, 192)) * 1e5).astype(np.float32)
+    q = (rng.standard_normal((100, 192)) * 1e5).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        tb.set_engine(tb.ENGINE_AUTO)
+        ti, te = t.search_batch(q, k=1)
+    oi, od = oracle.knn_f32(ds, q, 1)
+    assert np.array_equal(ti, oi) and np.array_equal(te, od)
+    # dataset in range, one query far outside it
+    ds = rng.standard_normal((500, 192)).astype(np.float32)
+    q = rng.standard_normal((100, 192)).astype(np.float32)
+    q[3] *= 1e6
+    with tb.KDTree.from_rows(ds) as t:
+        ti, te = t.search_batch(q, k=1)
+    oi, od = oracle.knn_f32(ds, q, 1)
+    assert np.array_equal(ti, oi) and np.array_equal(te, od)

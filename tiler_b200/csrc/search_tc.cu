@@ -1,9 +1,262 @@
-// search_tc.cu — tensor-core (tcgen05/TMEM/TMA) search.  Placeholder until the kernel lands:
-// datasets are prepared without the fp16 operand, so the engine dispatch never reaches here.
+// search_tc.cu — tensor-core FrameTiling search (sm_100a: tcgen05 + TMEM + TMA).
+//
+// Replaces the per-position exact 1-NN of DoFrameTiling (reference main.pas:4020-4038,
+// FFI ann_kdtree_search extern.pas:65) and the k = 8 pre-filter of UseOne (main.pas:3830).
+//
+// Coarse pass.  Rows and queries are centred on the dataset's column mean (distance-
+// invariant) and rounded to fp16; the kernel computes, for every (query, row),
+//     s~ = ||t~||^2 - 2 q~.t~  =  ||q~ - t~||^2 - ||q~||^2
+// as a dense contraction on the 5th-gen tensor cores: a persistent, warp-specialised CTA
+// per SM keeps a 256-query tile resident in shared memory (two M = 128 halves), streams
+// 128-row tileset tiles through a 6-deep TMA ring, issues tcgen05.mma (M128 N128 K16,
+// fp32 accumulate) into four TMEM accumulators (2 halves x 2 stages = 512 columns), and
+// eight epilogue warps read them back with tcgen05.ld (thread = query row) and keep each
+// query's KC smallest scores in registers.  The Q x N score matrix never reaches HBM.
+//
+// Exactness.  s~ + ||q~||^2 is the exact squared distance between the ROUNDED vectors up to
+// fp32 summation error, so by the triangle inequality every row that is not a candidate
+// has true distance >= (sqrt(tau + ||q~||^2 - a) - e)^2 with tau the largest kept score,
+// e = 2^-11 (||q'|| + max||t'||) + tiny and a the accumulation slack.  rerank.cu recomputes
+// the candidates in exact float32 (the reference's arithmetic), and queries whose k-th
+// best exact distance is not strictly below that bound are re-run on the exact SIMT
+// engine.  Results are therefore identical to the SIMT engine's, not approximately equal.
 #include "tm_common.cuh"
-int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) { (void)h; (void)s; return 0; }
+#include "ptx_sm100.cuh"
+#include "search_tc.h"
+#include <cudaTypedefs.h>
+#include <math.h>
+
+namespace {
+
+// ------------------------------------------------------------------ operand preparation
+constexpr int PREP_ROWS = 256; // rows per partial-sum block
+
+__global__ void colsum_partial_kernel(const float *__restrict__ rows, int64_t n, int dd, double *__restrict__ part) {
+    int64_t r0 = (int64_t)blockIdx.x * PREP_ROWS;
+    int64_t r1 = min(n, r0 + PREP_ROWS);
+    for (int j = threadIdx.x; j < dd; j += blockDim.x) {
+        double acc = 0.0;
+        for (int64_t r = r0; r < r1; r++) acc += (double)rows[r * dd + j];
+        part[(int64_t)blockIdx.x * dd + j] = acc;
+    }
+}
+
+__global__ void colmean_final_kernel(const double *__restrict__ part, int nblocks, int64_t n, int dd,
+                                     float *__restrict__ mean) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= dd) return;
+    double acc = 0.0;
+    for (int b = 0; b < nblocks; b++) acc += part[(int64_t)b * dd + j]; // fixed order: deterministic
+    mean[j] = n > 0 ? (float)(acc / (double)n) : 0.f;
+}
+
+// one warp per row: centred fp16 operand (zero padded to kp), ||t~||^2 (fp32 of the rounded
+// values, what the GEMM sees), exact-ish ||t'|| for the slack, range check for fp16
+__global__ void operand_kernel(const float *__restrict__ rows, int64_t n, int64_t n_pad, int dd, int kp,
+                               const float *__restrict__ mean, __half *__restrict__ out16,
+                               float *__restrict__ norm16, float *__restrict__ norm_exact, float pad_norm,
+                               unsigned int *__restrict__ max_norm_bits, unsigned int *__restrict__ max_abs_bits) {
+    int64_t r = (int64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x / 32);
+    int lane = threadIdx.x & 31;
+    if (r >= n_pad) return;
+    float s16 = 0.f, sex = 0.f, mabs = 0.f;
+    for (int j = lane; j < kp; j += 32) {
+        float v = 0.f;
+        if (r < n && j < dd) v = rows[r * dd + j] - mean[j];
+        __half h = __float2half_rn(v);
+        float hv = __half2float(h);
+        out16[r * kp + j] = h;
+        s16 += hv * hv;
+        sex += v * v;
+        mabs = fmaxf(mabs, fabsf(v));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s16 += __shfl_xor_sync(0xffffffffu, s16, o);
+        sex += __shfl_xor_sync(0xffffffffu, sex, o);
+        mabs = fmaxf(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
+    }
+    if (lane == 0) {
+        norm16[r] = (r < n) ? s16 : pad_norm;
+        if (norm_exact) norm_exact[r] = sqrtf(sex);
+        if (r < n) {
+            if (max_norm_bits) atomicMax(max_norm_bits, __float_as_uint(sqrtf(sex)));
+            if (max_abs_bits) atomicMax(max_abs_bits, __float_as_uint(mabs));
+        }
+    }
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    if (fn) return fn;
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+        return nullptr;
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    return fn;
+}
+
+// fp16 [rows][kp] row-major, box = 64 (K) x 128 (rows), SWIZZLE_128B
+int make_tmap(CUtensorMap *m, const __half *base, int64_t rows, int kp) {
+    auto enc = get_encode();
+    if (!enc) { tm_set_error("cuTensorMapEncodeTiled unavailable"); return TM_ECUDA; }
+    cuuint64_t dims[2] = {(cuuint64_t)kp, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)kp * sizeof(__half)};
+    cuuint32_t box[2] = {64, 128};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half *>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { tm_set_error("cuTensorMapEncodeTiled failed (%d)", (int)r); return TM_ECUDA; }
+    return 0;
+}
+
+} // namespace
+
+// Called at dataset creation (rows_f32 already queued on s).  Leaves rows_f16 == nullptr when
+// the tensor-core path does not apply (dd > 192, empty set, values outside the fp16 range).
+int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
+    h->rows_f16 = nullptr;
+    if (h->n < 1 || h->dd > 192) return 0;
+    const int kp = ((h->dd + 63) / 64) * 64;
+    const int64_t n_pad = ((h->n + 127) / 128) * 128;
+    const int nblocks = (int)((h->n + PREP_ROWS - 1) / PREP_ROWS);
+    double *part = nullptr;
+    unsigned int *mx = nullptr;
+    __half *r16 = nullptr;
+    TM_CUDA(cudaMalloc(&part, sizeof(double) * (size_t)nblocks * h->dd));
+    TM_CUDA(cudaMalloc(&mx, 2 * sizeof(unsigned int)));
+    TM_CUDA(cudaMalloc(&h->mean, sizeof(float) * h->dd));
+    TM_CUDA(cudaMalloc(&h->norms, sizeof(float) * n_pad));
+    TM_CUDA(cudaMalloc(&r16, sizeof(__half) * (size_t)n_pad * kp));
+    TM_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned int), s));
+    colsum_partial_kernel<<<nblocks, 192, 0, s>>>(h->rows_f32, h->n, h->dd, part);
+    colmean_final_kernel<<<(h->dd + 63) / 64, 64, 0, s>>>(part, nblocks, h->n, h->dd, h->mean);
+    operand_kernel<<<(unsigned)((n_pad + 7) / 8), 256, 0, s>>>(h->rows_f32, h->n, n_pad, h->dd, kp, h->mean, r16,
+                                                             h->norms, nullptr, INFINITY, mx, mx + 1);
+    tm_count_launch(3);
+    TM_CUDA(cudaGetLastError());
+    unsigned int hmx[2];
+    TM_CUDA(cudaMemcpyAsync(hmx, mx, sizeof hmx, cudaMemcpyDeviceToHost, s));
+    TM_CUDA(cudaStreamSynchronize(s));
+    cudaFree(part);
+    cudaFree(mx);
+    float max_norm, max_abs;
+    memcpy(&max_norm, &hmx[0], 4);
+    memcpy(&max_abs, &hmx[1], 4);
+    if (!(max_abs < 30000.f)) { // outside the comfortable fp16 range (or NaN): exact engine only
+        cudaFree(r16);
+        return 0;
+    }
+    h->rows_f16 = r16;
+    h->n_pad = n_pad;
+    h->kp = kp;
+    h->max_norm = max_norm;
+    h->tmap_rows = malloc(sizeof(CUtensorMap));
+    return make_tmap(static_cast<CUtensorMap *>(h->tmap_rows), r16, n_pad, kp);
+}
+
+int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, int64_t nq_pad, __half *d_q16,
+                            float *d_qnorm16, float *d_qnorm_exact, cudaStream_t s) {
+    operand_kernel<<<(unsigned)((nq_pad + 7) / 8), 256, 0, s>>>(d_q, nq, nq_pad, h->dd, h->kp, h->mean, d_q16,
+                                                              d_qnorm16, d_qnorm_exact, 0.f, nullptr, nullptr);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "operand_kernel(q)");
+}
+
+int tm_make_query_tmap(void *tmap, const __half *d_q16, int64_t nq_pad, int kp) {
+    return make_tmap(static_cast<CUtensorMap *>(tmap), d_q16, nq_pad, kp);
+}
+
+#include "search_tc_kernel.inc"
+
+// ------------------------------------------------------------------ host orchestration
+namespace {
+struct TcScratch {
+    __half *q16 = nullptr;
+    float *qn16 = nullptr, *qne = nullptr, *cand_s = nullptr;
+    int *cand_i = nullptr, *fb_list = nullptr, *fb_count = nullptr;
+    int *h_count = nullptr; // pinned
+    size_t cap_q = 0, cap_c = 0;
+    int kp = 0;
+    std::mutex mu;
+} g_tc;
+
+int ensure_tc_scratch(int64_t nq_pad, int kp, size_t cand_elems, cudaStream_t s) {
+    if ((size_t)nq_pad * kp > g_tc.cap_q * (size_t)(g_tc.kp ? g_tc.kp : 1) || kp != g_tc.kp || (size_t)nq_pad > g_tc.cap_q) {
+        cudaStreamSynchronize(s);
+        cudaFree(g_tc.q16); cudaFree(g_tc.qn16); cudaFree(g_tc.qne); cudaFree(g_tc.fb_list);
+        g_tc.q16 = nullptr; g_tc.cap_q = 0;
+        TM_CUDA(cudaMalloc(&g_tc.q16, sizeof(__half) * (size_t)nq_pad * kp));
+        TM_CUDA(cudaMalloc(&g_tc.qn16, sizeof(float) * nq_pad));
+        TM_CUDA(cudaMalloc(&g_tc.qne, sizeof(float) * nq_pad));
+        TM_CUDA(cudaMalloc(&g_tc.fb_list, sizeof(int) * nq_pad));
+        g_tc.cap_q = nq_pad;
+        g_tc.kp = kp;
+    }
+    if (cand_elems > g_tc.cap_c) {
+        cudaStreamSynchronize(s);
+        cudaFree(g_tc.cand_s); cudaFree(g_tc.cand_i);
+        g_tc.cand_s = nullptr; g_tc.cap_c = 0;
+        TM_CUDA(cudaMalloc(&g_tc.cand_s, sizeof(float) * cand_elems));
+        TM_CUDA(cudaMalloc(&g_tc.cand_i, sizeof(int) * cand_elems));
+        g_tc.cap_c = cand_elems;
+    }
+    if (!g_tc.fb_count) {
+        TM_CUDA(cudaMalloc(&g_tc.fb_count, sizeof(int)));
+        TM_CUDA(cudaMallocHost(&g_tc.h_count, sizeof(int)));
+    }
+    return 0;
+}
+} // namespace
+
 int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s) {
-    (void)h; (void)d_q; (void)nq; (void)k; (void)d_idx; (void)d_err; (void)s;
-    tm_set_error("tensor-core engine not built");
-    return TM_EINVAL;
+    if (!h->rows_f16 || k > 8 || ((uintptr_t)d_q & 15)) // outside the tensor-core path's envelope: exact engine
+        return tm_launch_search_simt(h->rows_f32, h->n, h->dd, d_q, nq, k, d_idx, d_err, s);
+    const int kc = (k <= 4) ? 8 : 16;
+    const int nch = h->kp / 64;
+    const int64_t nq_pad = ((nq + TC_QTILE - 1) / TC_QTILE) * TC_QTILE;
+    const int qblocks = (int)(nq_pad / TC_QTILE);
+    const int total_tiles = (int)(h->n_pad / TC_BN);
+    // small query counts: split the row range so that every SM gets several work items
+    int nsplit = 1;
+    const int want = 8 * tm_num_sms();
+    if (qblocks < want) nsplit = (want + qblocks - 1) / qblocks;
+    if (nsplit > total_tiles / 8) nsplit = total_tiles / 8;
+    if (nsplit > 16) nsplit = 16;
+    if (nsplit < 1) nsplit = 1;
+    int tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
+    nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
+
+    std::lock_guard<std::mutex> lk(g_tc.mu);
+    int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)nq_pad * nsplit * kc, s);
+    if (r) return r;
+    if ((r = tm_launch_query_operand(h, d_q, nq, nq_pad, g_tc.q16, g_tc.qn16, g_tc.qne, s))) return r;
+    CUtensorMap tq;
+    if ((r = make_tmap(&tq, g_tc.q16, nq_pad, h->kp))) return r;
+    const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
+    TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
+    int tok = tm_prof_begin(2, s);
+#define TC_LAUNCH(NCH, KC) launch_tc<NCH, KC>(tq, tt, h->norms, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, s)
+    if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8) : nch == 2 ? TC_LAUNCH(2, 8) : TC_LAUNCH(3, 8);
+    else r = nch == 1 ? TC_LAUNCH(1, 16) : nch == 2 ? TC_LAUNCH(2, 16) : TC_LAUNCH(3, 16);
+#undef TC_LAUNCH
+    tm_prof_end(tok, s);
+    if (r) return r;
+    tok = tm_prof_begin(3, s);
+    r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, nsplit, kc, g_tc.qn16, g_tc.qne,
+                         h->max_norm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
+    tm_prof_end(tok, s);
+    if (r) return r;
+    // queries the certificate rejected go through the exact engine (one host round trip for the count)
+    TM_CUDA(cudaMemcpyAsync(g_tc.h_count, g_tc.fb_count, sizeof(int), cudaMemcpyDeviceToHost, s));
+    TM_CUDA(cudaStreamSynchronize(s));
+    const int nfb = *g_tc.h_count;
+    if (nfb > 0) {
+        g_fallbacks.fetch_add(nfb, std::memory_order_relaxed);
+        r = tm_launch_search_simt_list(h->rows_f32, h->n, h->dd, d_q, g_tc.fb_list, nullptr, nfb, k, d_idx, d_err, s);
+    }
+    return r;
 }

@@ -66,10 +66,6 @@ int tm_launch_global_rows(const uint8_t *d_palpix, int64_t ntiles, float *d_out,
 
 // ---- dataset preparation (prep.cu): mean, centred fp16 operand, norms
 int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s);
-// query operand: centred fp16 rows + [1,1,1] tail, fp32 ||q-mu||^2
-int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, __half *d_q16,
-                            float *d_qnorm, cudaStream_t s);
-
 // ---- exact SIMT search (search_simt.cu): sequential fp32 accumulation, lowest index on ties
 int tm_launch_search_simt(const float *d_rows, int64_t n, int dd, const float *d_q, int64_t nq, int k,
                           int *d_idx, float *d_err, cudaStream_t s);
