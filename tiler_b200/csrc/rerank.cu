@@ -72,8 +72,9 @@ __global__ void __launch_bounds__(RR_QPB * 8) rerank_kernel(
     // certificate: no row outside the candidate lists can be at or below the k-th exact distance
     float tau = INFINITY;
     for (int sp = 0; sp < nsplit; sp++) tau = fminf(tau, cand_s[qg * C + sp * kc + kc - 1]);
-    bool ok = true;
-    if (tau < INFINITY) {
+    // NaN / overflowed fp16 query operands never certify (their scores are NaN and select nothing)
+    bool ok = qn16[qg] < 3.0e38f;
+    if (ok && tau < INFINITY) {
         const double nsum = (double)qne[qg] + (double)max_tnorm;
         const double a = 6e-5 * nsum * nsum + 1e-6;                   // fp32 accumulation slack
         const double e = nsum * (1.001 / 2048.0) + 1e-6;              // fp16 rounding of both vectors
