@@ -11,7 +11,7 @@ constexpr int RR_QPB = 16; // queries per block, 8 lanes each
 
 __global__ void __launch_bounds__(RR_QPB * 8) rerank_kernel(
     const float *__restrict__ rows, int dd, const float *__restrict__ q, int64_t nq,
-    const float *__restrict__ cand_s, const int *__restrict__ cand_i, int nsplit, int kc,
+    const float *__restrict__ cand_s, const int *__restrict__ cand_i, const float *__restrict__ cand_tau, int nsplit, int kc,
     const float *__restrict__ qn16, const float *__restrict__ qne, float max_tnorm, int k,
     int *__restrict__ idx, float *__restrict__ err, int *__restrict__ fb_list, int *__restrict__ fb_count) {
     extern __shared__ float sm[];
@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(RR_QPB * 8) rerank_kernel(
     }
     // certificate: no row outside the candidate lists can be at or below the k-th exact distance
     float tau = INFINITY;
-    for (int sp = 0; sp < nsplit; sp++) tau = fminf(tau, cand_s[qg * C + sp * kc + kc - 1]);
+    for (int sp = 0; sp < nsplit; sp++) tau = fminf(tau, cand_tau[qg * nsplit + sp]); // admission threshold at scan end
     // NaN / overflowed fp16 query operands never certify (their scores are NaN and select nothing)
     bool ok = qn16[qg] < 3.0e38f;
     if (ok && tau < INFINITY) {
@@ -90,12 +90,12 @@ __global__ void __launch_bounds__(RR_QPB * 8) rerank_kernel(
 } // namespace
 
 int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, const float *d_cand_s,
-                     const int *d_cand_i, int nsplit, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
+                     const int *d_cand_i, const float *d_cand_tau, int nsplit, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
                      float max_tnorm, int k, int *d_idx, float *d_err, int *d_fb_list, int *d_fb_count,
                      cudaStream_t s) {
     const size_t smem = (size_t)RR_QPB * nsplit * kc * 8;
     rerank_kernel<<<(unsigned)((nq + RR_QPB - 1) / RR_QPB), RR_QPB * 8, smem, s>>>(
-        d_rows, dd, d_q, nq, d_cand_s, d_cand_i, nsplit, kc, d_qnorm16, d_qnorm_exact, max_tnorm, k, d_idx, d_err,
+        d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, max_tnorm, k, d_idx, d_err,
         d_fb_list, d_fb_count);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "rerank_kernel");

@@ -176,7 +176,7 @@ int tm_make_query_tmap(void *tmap, const __half *d_q16, int64_t nq_pad, int kp) 
 namespace {
 struct TcScratch {
     __half *q16 = nullptr;
-    float *qn16 = nullptr, *qne = nullptr, *cand_s = nullptr;
+    float *qn16 = nullptr, *qne = nullptr, *cand_s = nullptr, *cand_tau = nullptr;
     int *cand_i = nullptr, *fb_list = nullptr, *fb_count = nullptr;
     int *h_count = nullptr; // pinned
     size_t cap_q = 0, cap_c = 0;
@@ -198,8 +198,9 @@ int ensure_tc_scratch(int64_t nq_pad, int kp, size_t cand_elems, cudaStream_t s)
     }
     if (cand_elems > g_tc.cap_c) {
         cudaStreamSynchronize(s);
-        cudaFree(g_tc.cand_s); cudaFree(g_tc.cand_i);
+        cudaFree(g_tc.cand_s); cudaFree(g_tc.cand_i); cudaFree(g_tc.cand_tau);
         g_tc.cand_s = nullptr; g_tc.cap_c = 0;
+        TM_CUDA(cudaMalloc(&g_tc.cand_tau, sizeof(float) * cand_elems));
         TM_CUDA(cudaMalloc(&g_tc.cand_s, sizeof(float) * cand_elems));
         TM_CUDA(cudaMalloc(&g_tc.cand_i, sizeof(int) * cand_elems));
         g_tc.cap_c = cand_elems;
@@ -239,14 +240,14 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
     const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
     TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
     int tok = tm_prof_begin(2, s);
-#define TC_LAUNCH(NCH, KC) launch_tc<NCH, KC>(tq, tt, h->norms, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, s)
+#define TC_LAUNCH(NCH, KC) launch_tc<NCH, KC>(tq, tt, h->norms, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s)
     if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8) : nch == 2 ? TC_LAUNCH(2, 8) : TC_LAUNCH(3, 8);
     else r = nch == 1 ? TC_LAUNCH(1, 16) : nch == 2 ? TC_LAUNCH(2, 16) : TC_LAUNCH(3, 16);
 #undef TC_LAUNCH
     tm_prof_end(tok, s);
     if (r) return r;
     tok = tm_prof_begin(3, s);
-    r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, nsplit, kc, g_tc.qn16, g_tc.qne,
+    r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, nsplit, kc, g_tc.qn16, g_tc.qne,
                          h->max_norm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
     tm_prof_end(tok, s);
     if (r) return r;
