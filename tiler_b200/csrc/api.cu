@@ -172,7 +172,7 @@ static ANNkdtree *new_handle(int64_t n, int dd) {
 
 static void free_handle(ANNkdtree *h) {
     if (!h) return;
-    cudaFree(h->rows_f32); cudaFree(h->rows_f16); cudaFree(h->norms); cudaFree(h->mean);
+    cudaFree(h->rows_f32); cudaFree(h->rows_f16); cudaFree(h->norms); cudaFree(h->norm_tiles); cudaFree(h->mean);
     cudaFree(h->d_q1); cudaFree(h->d_i1); cudaFree(h->d_e1);
     if (h->h_pin) cudaFreeHost(h->h_pin);
     free(h->tmap_rows);

@@ -55,7 +55,8 @@ __global__ void colmean_final_kernel(const double *__restrict__ part, int nblock
 __global__ void operand_kernel(const float *__restrict__ rows, int64_t n, int64_t n_pad, int dd, int kp,
                                const float *__restrict__ mean, __half *__restrict__ out16,
                                float *__restrict__ norm16, float *__restrict__ norm_exact, float pad_norm,
-                               unsigned int *__restrict__ max_norm_bits, unsigned int *__restrict__ max_abs_bits) {
+                               float out_scale, unsigned int *__restrict__ max_norm_bits,
+                               unsigned int *__restrict__ max_abs_bits) {
     int64_t r = (int64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x / 32);
     int lane = threadIdx.x & 31;
     if (r >= n_pad) return;
@@ -65,7 +66,7 @@ __global__ void operand_kernel(const float *__restrict__ rows, int64_t n, int64_
         if (r < n && j < dd) v = rows[r * dd + j] - mean[j];
         __half h = __float2half_rn(v);
         float hv = __half2float(h);
-        out16[r * kp + j] = h;
+        out16[r * kp + j] = __float2half_rn(out_scale * hv); // out_scale is a power of two: exact
         s16 += hv * hv;
         sex += v * v;
         mabs = fmaxf(mabs, fabsf(v));
@@ -81,9 +82,37 @@ __global__ void operand_kernel(const float *__restrict__ rows, int64_t n, int64_
         if (norm_exact) norm_exact[r] = sqrtf(sex);
         if (r < n) {
             if (max_norm_bits) atomicMax(max_norm_bits, __float_as_uint(sqrtf(sex)));
-            if (max_abs_bits) atomicMax(max_abs_bits, __float_as_uint(mabs));
+            if (max_abs_bits) {
+                atomicMax(max_abs_bits, __float_as_uint(mabs));
+                atomicMax(max_abs_bits + 1, __float_as_uint(s16));
+            }
         }
     }
+}
+
+// ||t~||^2 / S as three fp16 parts in K columns 0..2 of a [128 rows][16] K-major no-swizzle operand tile
+// (8-row x 16-byte core matrices: byte = (k/8)*2048 + (r/8)*128 + (r%8)*16 + (k%8)*2); one extra
+// tcgen05.mma against an all-[S,S,S,0..] A tile adds the norm to every accumulator column.
+__global__ void normtile_kernel(const float *__restrict__ norm16, int64_t n_pad, float inv_scale,
+                                __half *__restrict__ tiles) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_pad) return;
+    const float v = norm16[r] * inv_scale;
+    __half h0 = __float2half_rn(v), h1 = __float2half_rn(0.f), h2 = h1;
+    if (v < 60000.f) {
+        const float r1 = v - __half2float(h0);
+        h1 = __float2half_rn(r1);
+        h2 = __float2half_rn(r1 - __half2float(h1));
+    } else {
+        h0 = __ushort_as_half(0x7c00); // +inf: padding rows can never be admitted
+    }
+    __half *t = tiles + (r / 128) * 2048;
+    const int rr = (int)(r % 128);
+    uint4 lo = make_uint4(0, 0, 0, 0);
+    lo.x = (uint32_t)__half_as_ushort(h0) | ((uint32_t)__half_as_ushort(h1) << 16);
+    lo.y = (uint32_t)__half_as_ushort(h2);
+    *reinterpret_cast<uint4 *>(t + (rr / 8) * 64 + (rr % 8) * 8) = lo;                 // K core matrix 0
+    *reinterpret_cast<uint4 *>(t + 1024 + (rr / 8) * 64 + (rr % 8) * 8) = make_uint4(0, 0, 0, 0); // core 1
 }
 
 PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
@@ -127,18 +156,18 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     unsigned int *mx = nullptr;
     __half *r16 = nullptr;
     TM_CUDA(cudaMalloc(&part, sizeof(double) * (size_t)nblocks * h->dd));
-    TM_CUDA(cudaMalloc(&mx, 2 * sizeof(unsigned int)));
+    TM_CUDA(cudaMalloc(&mx, 3 * sizeof(unsigned int)));
     TM_CUDA(cudaMalloc(&h->mean, sizeof(float) * h->dd));
     TM_CUDA(cudaMalloc(&h->norms, sizeof(float) * n_pad));
     TM_CUDA(cudaMalloc(&r16, sizeof(__half) * (size_t)n_pad * kp));
-    TM_CUDA(cudaMemsetAsync(mx, 0, 2 * sizeof(unsigned int), s));
+    TM_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned int), s));
     colsum_partial_kernel<<<nblocks, 192, 0, s>>>(h->rows_f32, h->n, h->dd, part);
     colmean_final_kernel<<<(h->dd + 63) / 64, 64, 0, s>>>(part, nblocks, h->n, h->dd, h->mean);
     operand_kernel<<<(unsigned)((n_pad + 7) / 8), 256, 0, s>>>(h->rows_f32, h->n, n_pad, h->dd, kp, h->mean, r16,
-                                                             h->norms, nullptr, INFINITY, mx, mx + 1);
+                                                             h->norms, nullptr, INFINITY, -2.f, mx, mx + 1);
     tm_count_launch(3);
     TM_CUDA(cudaGetLastError());
-    unsigned int hmx[2];
+    unsigned int hmx[3];
     TM_CUDA(cudaMemcpyAsync(hmx, mx, sizeof hmx, cudaMemcpyDeviceToHost, s));
     TM_CUDA(cudaStreamSynchronize(s));
     cudaFree(part);
@@ -146,10 +175,20 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     float max_norm, max_abs;
     memcpy(&max_norm, &hmx[0], 4);
     memcpy(&max_abs, &hmx[1], 4);
-    if (!(max_abs < 30000.f)) { // outside the comfortable fp16 range (or NaN): exact engine only
+    float max_n16;
+    memcpy(&max_n16, &hmx[2], 4);
+    // norm scale S (power of two, representable in fp16) so that ||t~||^2 / S fits fp16
+    float S = 1.f;
+    while (max_n16 / S > 32768.f && S < 32768.f) S *= 2.f;
+    if (!(max_abs < 30000.f) || !(max_n16 / S < 60000.f)) { // outside the fp16 envelope (or NaN): exact engine only
         cudaFree(r16);
         return 0;
     }
+    TM_CUDA(cudaMalloc(&h->norm_tiles, (size_t)(n_pad / 128) * 4096));
+    normtile_kernel<<<(unsigned)((n_pad + 255) / 256), 256, 0, s>>>(h->norms, n_pad, 1.f / S, h->norm_tiles);
+    tm_count_launch();
+    TM_CUDA(cudaGetLastError());
+    h->norm_scale = S;
     h->rows_f16 = r16;
     h->n_pad = n_pad;
     h->kp = kp;
@@ -161,7 +200,7 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
 int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, int64_t nq_pad, __half *d_q16,
                             float *d_qnorm16, float *d_qnorm_exact, cudaStream_t s) {
     operand_kernel<<<(unsigned)((nq_pad + 7) / 8), 256, 0, s>>>(d_q, nq, nq_pad, h->dd, h->kp, h->mean, d_q16,
-                                                              d_qnorm16, d_qnorm_exact, 0.f, nullptr, nullptr);
+                                                              d_qnorm16, d_qnorm_exact, 0.f, 1.f, nullptr, nullptr);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "operand_kernel(q)");
 }
@@ -240,7 +279,7 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
     const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
     TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
     int tok = tm_prof_begin(2, s);
-#define TC_LAUNCH(NCH, KC) launch_tc<NCH, KC>(tq, tt, h->norms, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s)
+#define TC_LAUNCH(NCH, KC) launch_tc<NCH, KC>(tq, tt, h->norm_tiles, h->norm_scale, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s)
     if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8) : nch == 2 ? TC_LAUNCH(2, 8) : TC_LAUNCH(3, 8);
     else r = nch == 1 ? TC_LAUNCH(1, 16) : nch == 2 ? TC_LAUNCH(2, 16) : TC_LAUNCH(3, 16);
 #undef TC_LAUNCH

@@ -25,6 +25,8 @@ struct ANNkdtree {
     float *rows_f32;
     __half *rows_f16;
     float *norms;
+    __half *norm_tiles; // per 128-row tile: [||t~||^2 / S split in 3 fp16][zeros] as a no-swizzle UMMA operand image
+    float norm_scale;   // S
     float *mean;
     int64_t n_pad;
     int kp;
