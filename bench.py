@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU-baseline sample time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--frames", type=int, default=0, help="override the clip length (profiling runs only)")
     return ap.parse_args()
 
 
@@ -215,6 +216,8 @@ def run_b200(args, rank, world, local_rank):
     tb.set_engine({"auto": tb.ENGINE_AUTO, "simt": tb.ENGINE_SIMT, "tc": tb.ENGINE_TC}[args.engine])
 
     frames, pos, ntiles = WORKLOADS[args.workload]
+    if args.frames:
+        frames = args.frames
     nq = frames * pos  # per GPU (weak scaling)
     gen = torch.Generator(device=dev).manual_seed(0x42381337)
     tiles, pal = synth_tileset(torch, ntiles, 16, gen)

@@ -22,8 +22,13 @@ __global__ void __launch_bounds__(RR_QPB * 8) rerank_kernel(
     const int64_t qg = (int64_t)blockIdx.x * RR_QPB + ql;
     if (qg < nq) {
         const float *qq = q + qg * dd;
+        // Rows scored at or above the final admission threshold are covered by the certificate's lower
+        // bound exactly like rows that were never admitted: only the ones below it need exact distances.
+        float tau_min = INFINITY;
+        for (int sp = 0; sp < nsplit; sp++) tau_min = fminf(tau_min, cand_tau[qg * nsplit + sp]);
         for (int c = l8; c < C; c += 8) {
-            const int ri = cand_i[qg * C + c];
+            int ri = cand_i[qg * C + c];
+            if (!(cand_s[qg * C + c] < tau_min) && tau_min < INFINITY) ri = -1;
             float acc = INFINITY;
             if (ri >= 0) {
                 const float *row = rows + (int64_t)ri * dd;
