@@ -15,6 +15,7 @@
  */
 #ifndef TMANN_H
 #define TMANN_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -78,6 +79,12 @@ TM_API int tm_set_engine(int engine);
  * without it they synchronise the device on entry and their own stream on exit. */
 TM_API int tm_set_stream(void *cuda_stream);
 TM_API int tm_device_sync(void);
+
+/* Page-locked host memory for buffers handed to the h_* entry points (optional: pageable
+ * memory works, pinned memory lets the PCIe copies run asynchronously at full rate).
+ * The Pascal side would allocate its per-frame TRGBPixels staging through these. */
+TM_API void *tm_host_alloc(size_t bytes);
+TM_API void tm_host_free(void *p);
 
 /* Contiguous-row variant of ann_kdtree_create; rows may be host or device memory
  * (is_device != 0).  Replaces the per-row gather of main.pas:3757-3779. */

@@ -66,6 +66,16 @@ void tmo_nn1_blocked_f32(const float *data, int64_t n, int dd, const float *q,
                          int64_t nq, int32_t *idx, float *dist, int nthreads);
 int  tmo_max_threads(void);
 
+/* ---- kdtree_ref.c ---------------------------------------------------
+ * ANN's published kd-tree (standard split, bucket size bs, incremental box distance, leaf scan
+ * with early exit) as created by ann_kdtree_create(pa, n, dd, 1, ANN_KD_STD) main.pas:3779, 3961
+ * and searched with eps = 0 (main.pas:3830, 4027).  data is not copied. */
+struct tmo_kdtree;
+struct tmo_kdtree *tmo_kdtree_create(const float *data, int64_t n, int dd, int bs);
+void tmo_kdtree_destroy(struct tmo_kdtree *t);
+void tmo_kdtree_search(const struct tmo_kdtree *t, const float *q, int64_t nq, int k, int32_t *idx,
+                       float *dist, int nthreads, int64_t *stats);
+
 /* ---- kmodes_ref.c ---------------------------------------------------- */
 /* semantics: 0 = x86-64 asm (kmodes.pas:357-412), 1 = generic (kmodes.pas:239-250) */
 uint64_t tmo_dissim(const uint8_t *a, const uint8_t *b, int semantics);

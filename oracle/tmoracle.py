@@ -46,6 +46,8 @@ def _proto(lib):
     lib.tmo_max_threads.restype = C.c_int
     lib.tmo_prepare_tile_mirrors.restype = C.c_int
     lib.tmo_kmodes_row.restype = C.c_int
+    lib.tmo_kdtree_create.restype = C.c_void_p
+    lib.tmo_kdtree_destroy.argtypes = [C.c_void_p]
 
 
 _proto(_lib)
@@ -157,6 +159,33 @@ def nn1_blocked_f32(data, q, nthreads=0):
                              _p(q, C.c_float), i64(nq), _p(idx, C.c_int32), _p(dist, C.c_float),
                              int(nthreads))
     return idx, dist
+
+
+class KDTreeRef:
+    """ANN-style kd-tree (kdtree_ref.c): ann_kdtree_create(rows, n, dd, 1, ANN_KD_STD) + eps = 0 search."""
+
+    def __init__(self, data, bs=1):
+        self.data = np.ascontiguousarray(data, np.float32)  # kept alive: the tree does not copy rows
+        self._lib = _lib
+        self._h = C.c_void_p(_lib.tmo_kdtree_create(_p(self.data, C.c_float), i64(self.data.shape[0]),
+                                                    int(self.data.shape[1]), int(bs)))
+
+    def search(self, q, k=1, nthreads=0, with_stats=False):
+        q = np.ascontiguousarray(q, np.float32).reshape(-1, self.data.shape[1])
+        nq = q.shape[0]
+        idx = np.empty((nq, k), np.int32)
+        dist = np.empty((nq, k), np.float32)
+        st = np.zeros(2, np.int64)
+        self._lib.tmo_kdtree_search(self._h, _p(q, C.c_float), i64(nq), int(k), _p(idx, C.c_int32),
+                                    _p(dist, C.c_float), int(nthreads), _p(st, C.c_int64))
+        return (idx, dist, st) if with_stats else (idx, dist)
+
+    def close(self):
+        if self._h:
+            self._lib.tmo_kdtree_destroy(self._h)
+            self._h = None
+
+    __del__ = close
 
 
 # ---- kmodes -----------------------------------------------------------------

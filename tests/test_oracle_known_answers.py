@@ -223,3 +223,41 @@ def test_planted_queries_recovered(oracle):
     idx, d, _ = oracle.knn_f64(ds, q, 1)
     assert d[0, 0] == 0.0
     assert np.array_equal(ds[idx[0, 0]], ds[17 * 4 + 2])
+
+
+# ---- ANN-style kd-tree restatement vs the brute-force restatement (two independently written paths)
+def test_kdtree_matches_bruteforce_k1_and_k8(oracle, small_case):
+    o = oracle
+    ds = o.psyv_tileset_f32(small_case["tiles"], small_case["pal"])
+    q = o.psyv_queries_f32(small_case["rgb"])
+    kd = o.KDTreeRef(ds)
+    i1, d1, st = kd.search(q, 1, with_stats=True)
+    fi, fd = o.knn_f32(ds, q, 1)
+    assert np.array_equal(d1, fd)  # same float32 sequential sum => bit-identical distances
+    same = i1[:, 0] == fi[:, 0]
+    # a differing index is only legal among exact float32 ties (ANN's tie order is traversal order)
+    assert np.array_equal(d1[~same], fd[~same])
+    assert st[0] < len(q) * len(ds)  # pruning happened at all
+    i8, d8 = kd.search(q[:200], 8)
+    f8i, f8d = o.knn_f32(ds, q[:200], 8)
+    assert np.array_equal(d8, f8d)
+    kd.close()
+
+
+def test_kdtree_edge_cases(oracle):
+    o = oracle
+    rng = np.random.default_rng(3)
+    # duplicates, n < k, n = 1, stage-1 shaped integer rows (D = 64)
+    rows = rng.integers(0, 16, (37, 64)).astype(np.float32)
+    rows[5] = rows[20]
+    kd = o.KDTreeRef(rows)
+    i, d = kd.search(rows[20], 2)
+    assert set(i[0]) == {5, 20} and d[0, 0] == 0 and d[0, 1] == 0
+    i, d = kd.search(rows[:4], 8)
+    fi, fd = o.knn_f32(rows, rows[:4], 8)
+    assert np.array_equal(d, fd)
+    kd.close()
+    one = o.KDTreeRef(rows[:1])
+    i, d = one.search(rows[3], 3)
+    assert i[0, 0] == 0 and i[0, 1] == -1 and i[0, 2] == -1
+    one.close()

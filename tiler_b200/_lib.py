@@ -39,6 +39,8 @@ PROTOTYPES = {
     "tm_set_engine": (i32, [i32]),
     "tm_set_stream": (i32, [vp]),
     "tm_device_sync": (i32, []),
+    "tm_host_alloc": (vp, [C.c_size_t]),
+    "tm_host_free": (None, [vp]),
     "tm_dataset_create": (vp, [vp, i64, i32, i32]),
     "tm_dataset_rows": (i64, [vp]),
     "tm_dataset_dim": (i32, [vp]),

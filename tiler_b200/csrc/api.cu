@@ -3,6 +3,9 @@
 #include "tm_common.cuh"
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
+#include <chrono>
+#include <algorithm>
 #include <vector>
 
 std::atomic<int64_t> g_launches{0}, g_queries{0}, g_fallbacks{0};
@@ -315,6 +318,17 @@ int ann_kdtree_search_multi(ANNkdtree *akd, int *idxs, float *errs, int cnt, flo
     tm_set_error("ann_kdtree_search_multi: cnt > 16 unsupported");
     for (int j = 0; j < cnt; j++) { idxs[j] = -1; if (errs) errs[j] = 0.f; }
     return 0;
+}
+
+// pinned host memory for the caller's frame buffers (full-rate, asynchronous PCIe copies)
+void *tm_host_alloc(size_t bytes) {
+    if (tm_ensure_device()) return nullptr;
+    void *p = nullptr;
+    if (tm_check(cudaMallocHost(&p, bytes ? bytes : 1), "cudaMallocHost")) return nullptr;
+    return p;
+}
+void tm_host_free(void *p) {
+    if (p) cudaFreeHost(p);
 }
 
 int tm_get_stats(tm_stats *out) {
