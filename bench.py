@@ -242,28 +242,32 @@ def run_b200(args, rank, world, local_rank):
     if args.frames:
         frames = args.frames
     nq = frames * pos  # per GPU (weak scaling)
-    gen = torch.Generator(device=dev).manual_seed(0x42381337)
-    tiles, pal = synth_tileset(torch, ntiles, 16, gen)
-    if world > 1:  # one-time tileset broadcast over NCCL/NVLink; rank 0's tileset wins
-        dist.broadcast(tiles, 0)
-        dist.broadcast(pal, 0)
-    gen.manual_seed(0x42381337 + 1 + rank)
-    d_rgb = synth_queries(torch, nq, tiles, pal, gen)
+    from tiler_b200.shard import ShardedFrameTiling, frame_shards
+    gen = torch.Generator(device=dev).manual_seed(0x42381337 + (0 if rank == 0 else 977 * rank))
+    tiles, pal = synth_tileset(torch, ntiles, 16, gen)  # ranks > 0 start with a different set: the broadcast decides
+    pal = pal.view(1, -1).contiguous()
+    sft = ShardedFrameTiling()
+    # weak scaling: the clip is `world` times longer, rank r owns the contiguous whole-frame range r
+    shards = frame_shards(frames * world, pos, world)
+    assert shards[rank][1] - shards[rank][0] == nq
     torch.cuda.synchronize()
     t_ds0 = time.perf_counter()
-    tree = tb.KDTree.from_tileset(tiles, pal.view(1, -1))  # pack/mirror kernel + operand prep, on device
+    # one-time tileset broadcast over NCCL/NVLink (rank 0's tileset wins), then the
+    # pack/mirror kernel + operand prep on every GPU
+    tree = sft.broadcast_tileset(tiles, pal)
     torch.cuda.synchronize()
     dataset_build_ms = 1e3 * (time.perf_counter() - t_ds0)
+    gen.manual_seed(0x42381337 + 1 + rank)
+    d_rgb = synth_queries(torch, nq, tiles, pal.view(-1), gen)
+    torch.cuda.synchronize()
     d_idx = torch.empty(nq, dtype=torch.int32, device=dev)
     d_err = torch.empty(nq, dtype=torch.float32, device=dev)
-    gather_idx = [torch.empty_like(d_idx) for _ in range(world)] if (world > 1 and rank == 0) else None
-    gather_err = [torch.empty_like(d_err) for _ in range(world)] if (world > 1 and rank == 0) else None
+    sizes = [b - a for a, b in shards]
 
     def step():
-        tree.frametiling_search(d_rgb, out_idx=d_idx, out_err=d_err)
-        if world > 1:  # result gather (NCCL) is part of the step
-            dist.gather(d_idx, gather_idx, 0)
-            dist.gather(d_err, gather_err, 0)
+        sft.search_local(d_rgb, out_idx=d_idx, out_err=d_err)
+        if world > 1:  # result gather to rank 0 (NCCL) is part of the step
+            sft.gather_results(d_idx, d_err, sizes)
 
     def barrier():
         torch.cuda.synchronize()
@@ -355,10 +359,10 @@ def run_b200(args, rank, world, local_rank):
             line["e2e"] = e2e
         if not args.no_cpu_baseline and world == 1:
             m = 1 << 15
-            line["cpu_baseline"] = cpu_baseline(tiles.cpu().numpy(), pal.cpu().numpy(), d_rgb[:m].cpu().numpy(),
+            line["cpu_baseline"] = cpu_baseline(tiles.cpu().numpy(), pal.view(-1).cpu().numpy(), d_rgb[:m].cpu().numpy(),
                                                 args.cpu_seconds, d_idx[:m].cpu().numpy(), d_err[:m].cpu().numpy())
         print(json.dumps(line))
-    tree.destroy()
+    sft.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
