@@ -159,6 +159,7 @@ def cpu_baseline(tiles_np, pal_np, rgb_sample_np, target_s, check_idx=None, chec
         o.use_native()
     except Exception:
         pass
+    o.set_threads(os.cpu_count() or 1)  # all host cores, whatever OMP_NUM_THREADS the launcher exported
     cores = o.max_threads()
     ds = o.psyv_tileset_f32(tiles_np, pal_np)
     fns, kd = _cpu_search_fns(o, ds)
@@ -192,6 +193,7 @@ def run_reference(args, rank, world):
         o.use_native()
     except Exception:
         pass
+    o.set_threads(os.cpu_count() or 1)  # torchrun exports OMP_NUM_THREADS=1: use all host cores anyway
     ds = o.psyv_tileset_f32(tiles.numpy(), pal.numpy())
     cap = 1 << 16
     rgb = synth_queries(torch, cap, tiles, pal, gen).numpy()

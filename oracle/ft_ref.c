@@ -23,6 +23,16 @@ int tmo_max_threads(void) {
 #endif
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU baseline resets the team size
+ * to the host's core count explicitly. */
+void tmo_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* insert (d,i) into ascending list of length k+1 (extra slot = next distance);
  * strict < keeps the lowest index among equal distances. */
 static inline void ins_f64(double *bd, int32_t *bi, int k1, double d, int32_t i) {

@@ -65,6 +65,7 @@ void tmo_knn_f32(const float *data, int64_t n, int dd, const float *q, int64_t n
 void tmo_nn1_blocked_f32(const float *data, int64_t n, int dd, const float *q,
                          int64_t nq, int32_t *idx, float *dist, int nthreads);
 int  tmo_max_threads(void);
+void tmo_set_threads(int n);
 
 /* ---- kdtree_ref.c ---------------------------------------------------
  * ANN's published kd-tree (standard split, bucket size bs, incremental box distance, leaf scan

@@ -58,6 +58,11 @@ def max_threads():
     return int(_lib.tmo_max_threads())
 
 
+def set_threads(n):
+    """OpenMP team size of the oracle (torchrun forces OMP_NUM_THREADS=1 on its workers)."""
+    _lib.tmo_set_threads(int(n))
+
+
 def rgb_to_yuv(r, g, b, gamma=-1):
     y, u, v = C.c_double(), C.c_double(), C.c_double()
     _lib.tmo_rgb_to_yuv(int(r), int(g), int(b), int(gamma), C.byref(y), C.byref(u), C.byref(v))
