@@ -279,9 +279,10 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
     const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
     TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
     int tok = tm_prof_begin(2, s);
-#define TC_LAUNCH(NCH, KC) launch_tc<NCH, KC>(tq, tt, h->norm_tiles, h->norm_scale, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s)
-    if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8) : nch == 2 ? TC_LAUNCH(2, 8) : TC_LAUNCH(3, 8);
-    else r = nch == 1 ? TC_LAUNCH(1, 16) : nch == 2 ? TC_LAUNCH(2, 16) : TC_LAUNCH(3, 16);
+#define TC_LAUNCH(NCH, KC, K1) launch_tc<NCH, KC, K1>(tq, tt, h->norm_tiles, h->norm_scale, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s)
+    if (k == 1) r = nch == 1 ? TC_LAUNCH(1, 8, true) : nch == 2 ? TC_LAUNCH(2, 8, true) : TC_LAUNCH(3, 8, true);
+    else if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8, false) : nch == 2 ? TC_LAUNCH(2, 8, false) : TC_LAUNCH(3, 8, false);
+    else r = nch == 1 ? TC_LAUNCH(1, 16, false) : nch == 2 ? TC_LAUNCH(2, 16, false) : TC_LAUNCH(3, 16, false);
 #undef TC_LAUNCH
     tm_prof_end(tok, s);
     if (r) return r;
