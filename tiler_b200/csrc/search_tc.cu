@@ -142,6 +142,22 @@ int make_tmap(CUtensorMap *m, const __half *base, int64_t rows, int kp) {
     return 0;
 }
 
+// norm-tile images as a 2-D tensor: fp16 [tiles * 8][256], box = 256 x 8 = one 4 KB image (used by the
+// CTA-pair kernel, whose loads must be tensor copies to signal the leader CTA's barrier)
+int make_tmap_norm(CUtensorMap *m, const __half *base, int64_t tiles) {
+    auto enc = get_encode();
+    if (!enc) { tm_set_error("cuTensorMapEncodeTiled unavailable"); return TM_ECUDA; }
+    cuuint64_t dims[2] = {256, (cuuint64_t)tiles * 8};
+    cuuint64_t strides[1] = {256 * sizeof(__half)};
+    cuuint32_t box[2] = {256, 8};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half *>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { tm_set_error("cuTensorMapEncodeTiled(norm tiles) failed (%d)", (int)r); return TM_ECUDA; }
+    return 0;
+}
+
 } // namespace
 
 // Called at dataset creation (rows_f32 already queued on s).  Leaves rows_f16 == nullptr when
@@ -150,7 +166,7 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     h->rows_f16 = nullptr;
     if (h->n < 1 || h->dd > 192) return 0;
     const int kp = ((h->dd + 63) / 64) * 64;
-    const int64_t n_pad = ((h->n + 127) / 128) * 128;
+    const int64_t n_pad = ((h->n + 255) / 256) * 256; // whole 256-row tiles of the CTA-pair kernel
     const int nblocks = (int)((h->n + PREP_ROWS - 1) / PREP_ROWS);
     double *part = nullptr;
     unsigned int *mx = nullptr;
@@ -193,8 +209,10 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     h->n_pad = n_pad;
     h->kp = kp;
     h->max_norm = max_norm;
-    h->tmap_rows = malloc(sizeof(CUtensorMap));
-    return make_tmap(static_cast<CUtensorMap *>(h->tmap_rows), r16, n_pad, kp);
+    h->tmap_rows = malloc(2 * sizeof(CUtensorMap)); // [0] rows_f16, [1] norm tiles
+    int r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows), r16, n_pad, kp);
+    if (!r) r = make_tmap_norm(static_cast<CUtensorMap *>(h->tmap_rows) + 1, h->norm_tiles, n_pad / 128);
+    return r;
 }
 
 int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, int64_t nq_pad, __half *d_q16,
@@ -210,6 +228,7 @@ int tm_make_query_tmap(void *tmap, const __half *d_q16, int64_t nq_pad, int kp) 
 }
 
 #include "search_tc_kernel.inc"
+#include "search_tc2_kernel.inc"
 
 // ------------------------------------------------------------------ host orchestration
 namespace {
@@ -259,35 +278,44 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
     const int nch = h->kp / 64;
     const int64_t nq_pad = ((nq + TC_QTILE - 1) / TC_QTILE) * TC_QTILE;
     const int qblocks = (int)(nq_pad / TC_QTILE);
-    const int total_tiles = (int)(h->n_pad / TC_BN);
+    // CTA-pair kernel (default) walks 256-row tiles and keeps two candidate lists per query and row split
+    // (one per accumulator column half); TM_TC_PAIR=0 selects the single-CTA kernel (128-row tiles).
+    static const bool pair = !(getenv("TM_TC_PAIR") && atoi(getenv("TM_TC_PAIR")) == 0);
+    const int tile_rows = pair ? T2_BN : TC_BN;
+    const int total_tiles = (int)(h->n_pad / tile_rows);
     // small query counts: split the row range so that every SM gets several work items
     int nsplit = 1;
-    const int want = 8 * tm_num_sms();
+    const int want = pair ? 4 * tm_num_sms() : 8 * tm_num_sms();
     if (qblocks < want) nsplit = (want + qblocks - 1) / qblocks;
-    if (nsplit > total_tiles / 8) nsplit = total_tiles / 8;
-    if (nsplit > 16) nsplit = 16;
+    if (nsplit > total_tiles / 4) nsplit = total_tiles / 4;
+    if (nsplit > (pair ? 8 : 16)) nsplit = pair ? 8 : 16;
     if (nsplit < 1) nsplit = 1;
     int tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
     nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
+    const int nlists = pair ? 2 * nsplit : nsplit;
 
     std::lock_guard<std::mutex> lk(g_tc.mu);
-    int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)nq_pad * nsplit * kc, s);
+    int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)nq_pad * nlists * kc, s);
     if (r) return r;
     if ((r = tm_launch_query_operand(h, d_q, nq, nq_pad, g_tc.q16, g_tc.qn16, g_tc.qne, s))) return r;
     CUtensorMap tq;
     if ((r = make_tmap(&tq, g_tc.q16, nq_pad, h->kp))) return r;
     const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
+    const CUtensorMap &tn = static_cast<const CUtensorMap *>(h->tmap_rows)[1];
     TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
     int tok = tm_prof_begin(2, s);
-#define TC_LAUNCH(NCH, KC, K1) launch_tc<NCH, KC, K1>(tq, tt, h->norm_tiles, h->norm_scale, qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s)
+#define TC_ARGS qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s
+#define TC_LAUNCH(NCH, KC, K1) (pair ? launch_tc2<NCH, KC, K1>(tq, tt, tn, h->norm_scale, TC_ARGS) \
+                                     : launch_tc<NCH, KC, K1>(tq, tt, h->norm_tiles, h->norm_scale, TC_ARGS))
     if (k == 1) r = nch == 1 ? TC_LAUNCH(1, 8, true) : nch == 2 ? TC_LAUNCH(2, 8, true) : TC_LAUNCH(3, 8, true);
     else if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8, false) : nch == 2 ? TC_LAUNCH(2, 8, false) : TC_LAUNCH(3, 8, false);
     else r = nch == 1 ? TC_LAUNCH(1, 16, false) : nch == 2 ? TC_LAUNCH(2, 16, false) : TC_LAUNCH(3, 16, false);
 #undef TC_LAUNCH
+#undef TC_ARGS
     tm_prof_end(tok, s);
     if (r) return r;
     tok = tm_prof_begin(3, s);
-    r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, nsplit, kc, g_tc.qn16, g_tc.qne,
+    r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, nlists, kc, g_tc.qn16, g_tc.qne,
                          h->max_norm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
     tm_prof_end(tok, s);
     if (r) return r;
