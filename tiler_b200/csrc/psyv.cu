@@ -24,7 +24,7 @@ struct PsyvTables {      // host-built, mirrors InitLuts main.pas:592-623
 };
 
 struct PsyvConsts {
-    double cu, cv, luma_div, haar;
+    double cu, cv, luma_div, luma_rcp, haar;
 };
 
 __device__ double *g_dct_lut_dev = nullptr; // unused placeholder (lut passed by pointer)
@@ -63,7 +63,13 @@ __device__ __forceinline__ void haar_level(double (&a)[64], double f) {
 __device__ __forceinline__ double plane_value(int32_t col, int plane, const PsyvTables *T,
                                               const PsyvConsts &K) {
     int r = col & 0xff, g = (col >> 8) & 0xff, b = (col >> 16) & 0xff; // FromRGB main.pas:571-576
-    double y = ((T->fr[r] + T->fg[g]) + T->fb[b]) / K.luma_div;         // main.pas:2674
+    // main.pas:2674 divides by cLumaDiv = 10000.  x / d is formed as q = RN(x * RN(1/d)), r = x - q*d (exact,
+    // fma), RN(q + r * RN(1/d)): three FP64 operations instead of the ~15-instruction division sequence,
+    // and bit-identical to the IEEE quotient for every value the three LUT sums can take (all 3 x 2^24
+    // (r, g, b, gamma) combinations were checked exhaustively on the host against x / 10000.0).
+    const double x = (T->fr[r] + T->fg[g]) + T->fb[b];
+    const double q0 = x * K.luma_rcp;
+    const double y = fma(fma(-q0, K.luma_div, x), K.luma_rcp, q0);
     if (plane == 0) return y;
     if (plane == 1) return (T->f[b] - y) * K.cu;                         // main.pas:2675
     return (T->f[r] - y) * K.cv;                                         // main.pas:2676
@@ -89,39 +95,73 @@ __device__ __forceinline__ void dct_plane(const double (&a)[64], const double *l
     }
 }
 
+// Shared-memory staging of one block's 64 tiles: the block's input (64 x 256 B) and output
+// (64 x 768 B) are both contiguous in global memory, so they move with fully coalesced 16-byte
+// accesses, while each thread reads / writes its own (tile, plane) slice in shared memory.  Row
+// strides are padded to 4 (mod 32) words so the 16-byte per-thread accesses are bank-conflict free.
+constexpr int PQ_TILES = 64;
+constexpr int PQ_IN_STRIDE = 68;   // words per staged input tile (64 + 4)
+constexpr int PQ_OUT_STRIDE = 196; // words per staged output row (192 + 4)
+constexpr size_t PQ_SMEM = sizeof(PsyvTables) + (size_t)PQ_TILES * (PQ_IN_STRIDE + PQ_OUT_STRIDE) * 4;
+
+__device__ __forceinline__ void store_row_smem(float *dst, const double (&a)[64]) {
+    float4 *d4 = reinterpret_cast<float4 *>(dst);
+#pragma unroll
+    for (int i = 0; i < 16; i++)
+        d4[i] = make_float4((float)a[4 * i], (float)a[4 * i + 1], (float)a[4 * i + 2], (float)a[4 * i + 3]);
+}
+
 template <bool WAVELETS>
 __global__ void __launch_bounds__(192) psyv_queries_kernel(const int32_t *__restrict__ rgb, int64_t nq,
                                                             const PsyvTables *__restrict__ tabs,
                                                             PsyvConsts K, const double *__restrict__ lut,
                                                             const double *__restrict__ qw,
                                                             float *__restrict__ out) {
-    __shared__ PsyvTables T;
+    extern __shared__ __align__(16) uint8_t psm[];
+    PsyvTables &T = *reinterpret_cast<PsyvTables *>(psm);
+    int32_t *sin = reinterpret_cast<int32_t *>(psm + sizeof(PsyvTables));
+    float *sout = reinterpret_cast<float *>(sin + PQ_TILES * PQ_IN_STRIDE);
+    const int64_t q0 = (int64_t)blockIdx.x * PQ_TILES;
+    const int ntile = (int)min((int64_t)PQ_TILES, nq - q0);
     for (int i = threadIdx.x; i < (int)(sizeof(PsyvTables) / 8); i += blockDim.x)
         reinterpret_cast<double *>(&T)[i] = reinterpret_cast<const double *>(tabs)[i];
-    __syncthreads();
-    // 64 tiles per block; lanes of a warp take consecutive tiles of ONE plane so the
-    // plane branch is warp-uniform (192 threads = 3 planes x 64 tiles).
-    int plane = threadIdx.x / 64;
-    int64_t q = (int64_t)blockIdx.x * 64 + (threadIdx.x & 63);
-    if (q >= nq) return;
-    const int4 *src = reinterpret_cast<const int4 *>(rgb + q * 64);
-    double a[64];
-#pragma unroll
-    for (int i = 0; i < 16; i++) {
-        int4 v = __ldg(src + i);
-        a[4 * i + 0] = plane_value(v.x, plane, &T, K);
-        a[4 * i + 1] = plane_value(v.y, plane, &T, K);
-        a[4 * i + 2] = plane_value(v.z, plane, &T, K);
-        a[4 * i + 3] = plane_value(v.w, plane, &T, K);
+    {   // coalesced load of the block's tiles (16 int4 per tile)
+        const int4 *src = reinterpret_cast<const int4 *>(rgb + q0 * 64);
+        for (int e = threadIdx.x; e < ntile * 16; e += blockDim.x)
+            *reinterpret_cast<int4 *>(sin + (e >> 4) * PQ_IN_STRIDE + (e & 15) * 4) = __ldg(src + e);
     }
-    float *dst = out + q * TM_DCT + plane * 64;
-    if (WAVELETS) {
-        haar_level<8>(a, K.haar);
-        haar_level<4>(a, K.haar);
-        haar_level<2>(a, K.haar);
-        store_row_f32(dst, a);
-    } else {
-        dct_plane(a, lut, qw, plane, dst);
+    __syncthreads();
+    // lanes of a warp take consecutive tiles of ONE plane so the plane branch is warp-uniform
+    // (192 threads = 3 planes x 64 tiles)
+    const int plane = threadIdx.x / 64, tl = threadIdx.x & 63;
+    if (tl < ntile) {
+        const int4 *src = reinterpret_cast<const int4 *>(sin + tl * PQ_IN_STRIDE);
+        double a[64];
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const int4 v = src[i];
+            a[4 * i + 0] = plane_value(v.x, plane, &T, K);
+            a[4 * i + 1] = plane_value(v.y, plane, &T, K);
+            a[4 * i + 2] = plane_value(v.z, plane, &T, K);
+            a[4 * i + 3] = plane_value(v.w, plane, &T, K);
+        }
+        float *dst = sout + tl * PQ_OUT_STRIDE + plane * 64;
+        if (WAVELETS) {
+            haar_level<8>(a, K.haar);
+            haar_level<4>(a, K.haar);
+            haar_level<2>(a, K.haar);
+            store_row_smem(dst, a);
+        } else {
+            dct_plane(a, lut, qw, plane, dst);
+        }
+    }
+    __syncthreads();
+    {   // coalesced store of the block's rows (48 float4 per row)
+        float4 *dst = reinterpret_cast<float4 *>(out + q0 * TM_DCT);
+        for (int e = threadIdx.x; e < ntile * 48; e += blockDim.x) {
+            const int t = e / 48, j = e - t * 48;
+            dst[e] = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + j * 4);
+        }
     }
 }
 
@@ -270,6 +310,7 @@ PsyvConsts make_consts() {
     K.cu = 0.5 / (1.0 - 722.0 / luma);
     K.cv = 0.5 / (1.0 - 2126.0 / luma);
     K.luma_div = luma;
+    K.luma_rcp = 1.0 / luma;
     K.haar = 1.0 / sqrt(2.0);
     return K;
 }
@@ -285,10 +326,16 @@ int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamm
     PsyvConsts K = make_consts();
     unsigned grid = (unsigned)((nq + 63) / 64);
     const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
+    static bool attr = false;
+    if (!attr) {
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM));
+        attr = true;
+    }
     if (flags & TM_PSYV_WAVELETS)
-        psyv_queries_kernel<true><<<grid, 192, 0, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+        psyv_queries_kernel<true><<<grid, 192, PQ_SMEM, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
     else
-        psyv_queries_kernel<false><<<grid, 192, 0, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+        psyv_queries_kernel<false><<<grid, 192, PQ_SMEM, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "psyv_queries_kernel");
 }

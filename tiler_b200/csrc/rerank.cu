@@ -7,78 +7,155 @@
 
 namespace {
 
-constexpr int RR_QPB = 16; // queries per block, 8 lanes each
+constexpr int RR_THREADS = 128; // one thread per query
+constexpr int RR_MAXV = 64;     // candidates below the final threshold a query may carry (more -> exact engine)
+constexpr int RR_K = 8;         // the tensor-core path serves k <= 8
 
-__global__ void __launch_bounds__(RR_QPB * 8) rerank_kernel(
+// exact float32 squared distance, one sequential add chain in dimension order, no FMA (-fmad=false):
+// the arithmetic of search_simt.cu and of the reference's ANN leaf scan
+__device__ __forceinline__ float exact_dist(const float *__restrict__ qq, const float *__restrict__ row, int dd) {
+    float acc = 0.f;
+    if ((dd & 3) == 0) {
+        const float4 *q4 = reinterpret_cast<const float4 *>(qq);
+        const float4 *r4 = reinterpret_cast<const float4 *>(row);
+#pragma unroll 4
+        for (int j = 0; j < dd / 4; j++) {
+            const float4 a = q4[j], b = __ldg(r4 + j);
+            float t0 = a.x - b.x; acc = acc + t0 * t0;
+            float t1 = a.y - b.y; acc = acc + t1 * t1;
+            float t2 = a.z - b.z; acc = acc + t2 * t2;
+            float t3 = a.w - b.w; acc = acc + t3 * t3;
+        }
+    } else {
+        for (int j = 0; j < dd; j++) {
+            float t = qq[j] - __ldg(row + j);
+            acc = acc + t * t;
+        }
+    }
+    return acc;
+}
+
+// Thread = query.  Pass 1 compacts the row ids of the candidates that scored below the final admission
+// threshold (usually one or two of the nlists * kc slots) into a per-thread shared-memory list; pass 2
+// walks that list in rounds, so a warp executes the 192-step distance chain max-over-lanes(count)
+// times with every lane busy.  In a round the warp stages, 32 dimensions at a time, the matching
+// 128-byte segments of its 32 query rows and 32 candidate rows in shared memory with cooperative
+// 16-byte loads (8 lanes per row segment: full sectors, no L1 thrash), then every lane runs the
+// sequential add chain over its own segment pair.
+constexpr int RR_SEG = 32;            // dimensions per staged segment
+constexpr int RR_SEG_STRIDE = 36;     // floats per staged row segment (pad: conflict-free 16-byte reads)
+
+template <bool K1, bool STAGED>
+__global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     const float *__restrict__ rows, int dd, const float *__restrict__ q, int64_t nq,
-    const float *__restrict__ cand_s, const int *__restrict__ cand_i, const float *__restrict__ cand_tau, int nsplit, int kc,
+    const float *__restrict__ cand_s, const int *__restrict__ cand_i, const float *__restrict__ cand_tau, int nlists, int kc,
     const float *__restrict__ qn16, const float *__restrict__ qne, float max_tnorm, int k,
     int *__restrict__ idx, float *__restrict__ err, int *__restrict__ fb_list, int *__restrict__ fb_count) {
-    extern __shared__ float sm[];
-    const int C = nsplit * kc;
-    float *sd = sm;                                        // [RR_QPB][C]
-    int *si = reinterpret_cast<int *>(sm + RR_QPB * C);   // [RR_QPB][C]
-    const int ql = threadIdx.x >> 3, l8 = threadIdx.x & 7;
-    const int64_t qg = (int64_t)blockIdx.x * RR_QPB + ql;
-    if (qg < nq) {
-        const float *qq = q + qg * dd;
-        // Rows scored at or above the final admission threshold are covered by the certificate's lower
-        // bound exactly like rows that were never admitted: only the ones below it need exact distances.
-        float tau_min = INFINITY;
-        for (int sp = 0; sp < nsplit; sp++) tau_min = fminf(tau_min, cand_tau[qg * nsplit + sp]);
-        for (int c = l8; c < C; c += 8) {
-            int ri = cand_i[qg * C + c];
-            if (!(cand_s[qg * C + c] < tau_min) && tau_min < INFINITY) ri = -1;
-            float acc = INFINITY;
-            if (ri >= 0) {
-                const float *row = rows + (int64_t)ri * dd;
-                acc = 0.f;
-                if ((dd & 3) == 0) { // 128-bit loads, still one sequential add chain in dimension order
-                    const float4 *q4 = reinterpret_cast<const float4 *>(qq);
-                    const float4 *r4 = reinterpret_cast<const float4 *>(row);
-                    for (int j = 0; j < dd / 4; j++) {
-                        const float4 a = q4[j], b = __ldg(r4 + j);
+    __shared__ uint8_t vlist[RR_MAXV][RR_THREADS]; // slot positions (< nlists * kc <= 256) of the live candidates
+    __shared__ __align__(16) float seg[STAGED ? RR_THREADS / 32 : 1][2][32 * RR_SEG_STRIDE];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t qg = (int64_t)blockIdx.x * RR_THREADS + threadIdx.x;
+    const bool live = qg < nq;
+    const int64_t qc = live ? qg : nq - 1; // clamped: dead lanes still help with the cooperative loads
+    const int C = nlists * kc;
+    // Rows scored at or above the final admission threshold are covered by the certificate's lower bound
+    // exactly like rows that were never admitted: only the ones below it need exact distances.
+    float tau = INFINITY;
+    int cnt = 0;
+    bool overflow = false;
+    if (live) {
+        for (int l = 0; l < nlists; l++) tau = fminf(tau, cand_tau[qg * nlists + l]);
+        const int4 *ci4 = reinterpret_cast<const int4 *>(cand_i + qg * C);
+        const float4 *cs4 = reinterpret_cast<const float4 *>(cand_s + qg * C);
+        for (int c4 = 0; c4 < C / 4; c4++) { // kc is 8 or 16: C is a multiple of 4, the lists are 16-byte aligned
+            const int4 ri = ci4[c4];
+            const float4 sc = cs4[c4];
+            const int r[4] = {ri.x, ri.y, ri.z, ri.w};
+            const float s[4] = {sc.x, sc.y, sc.z, sc.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++)
+                if (r[e] >= 0 && (s[e] < tau || !(tau < INFINITY))) {
+                    if (cnt < RR_MAXV) vlist[cnt][threadIdx.x] = (uint8_t)(c4 * 4 + e); else overflow = true;
+                    cnt++;
+                }
+        }
+        if (cnt > RR_MAXV) cnt = RR_MAXV;
+    }
+    float bd[K1 ? 1 : RR_K];
+    int bi[K1 ? 1 : RR_K];
+#pragma unroll
+    for (int j = 0; j < (K1 ? 1 : RR_K); j++) { bd[j] = INFINITY; bi[j] = 0x7fffffff; }
+    const int rounds = STAGED ? __reduce_max_sync(0xffffffffu, cnt) : cnt;
+    for (int v = 0; v < rounds; v++) {
+        const bool act = v < cnt;
+        const int ri = act ? __ldg(cand_i + qg * C + vlist[v][threadIdx.x]) : 0;
+        float d;
+        if (STAGED) {
+            float acc = 0.f;
+            float *sq = seg[warp][0], *sr = seg[warp][1];
+            for (int j0 = 0; j0 < dd; j0 += RR_SEG) {
+                const int seg4 = min(RR_SEG, dd - j0) >> 2; // float4 per row segment (dd % 4 == 0)
+                __syncwarp();
+                for (int e = lane; e < 32 * 8; e += 32) { // 8 float4 slots per row, 32 rows
+                    const int rr = e >> 3, f = e & 7;
+                    const int64_t qrow = __shfl_sync(0xffffffffu, qc, rr);
+                    const int crow = __shfl_sync(0xffffffffu, ri, rr);
+                    if (f < seg4) {
+                        *reinterpret_cast<float4 *>(sq + rr * RR_SEG_STRIDE + f * 4) =
+                            __ldg(reinterpret_cast<const float4 *>(q + qrow * dd + j0) + f);
+                        *reinterpret_cast<float4 *>(sr + rr * RR_SEG_STRIDE + f * 4) =
+                            __ldg(reinterpret_cast<const float4 *>(rows + (int64_t)crow * dd + j0) + f);
+                    }
+                }
+                __syncwarp();
+                const float4 *a4 = reinterpret_cast<const float4 *>(sq + lane * RR_SEG_STRIDE);
+                const float4 *b4 = reinterpret_cast<const float4 *>(sr + lane * RR_SEG_STRIDE);
+#pragma unroll
+                for (int f = 0; f < RR_SEG / 4; f++)
+                    if (f < seg4) { // one sequential add chain in dimension order, no FMA
+                        const float4 a = a4[f], b = b4[f];
                         float t0 = a.x - b.x; acc = acc + t0 * t0;
                         float t1 = a.y - b.y; acc = acc + t1 * t1;
                         float t2 = a.z - b.z; acc = acc + t2 * t2;
                         float t3 = a.w - b.w; acc = acc + t3 * t3;
                     }
-                } else {
-                    for (int j = 0; j < dd; j++) { // sequential, no FMA: matches search_simt.cu
-                        float t = qq[j] - __ldg(row + j);
-                        acc = acc + t * t;
-                    }
-                }
             }
-            sd[ql * C + c] = acc;
-            si[ql * C + c] = ri >= 0 ? ri : 0x7fffffff;
-        }
-    }
-    __syncthreads();
-    if (qg >= nq || l8 != 0) return;
-    // k smallest by (distance, index); C is small
-    float *d = sd + ql * C;
-    int *ii = si + ql * C;
-    float dk = 0.f;
-    for (int r = 0; r < k; r++) {
-        int bp = -1;
-        float bd = INFINITY;
-        int bi = 0x7fffffff;
-        for (int c = 0; c < C; c++) {
-            if (ii[c] == 0x7fffffff) continue;
-            if (d[c] < bd || (d[c] == bd && ii[c] < bi)) { bd = d[c]; bi = ii[c]; bp = c; }
-        }
-        if (bp >= 0) {
-            idx[qg * k + r] = bi; err[qg * k + r] = bd; ii[bp] = 0x7fffffff; dk = bd;
+            d = acc;
         } else {
-            idx[qg * k + r] = -1; err[qg * k + r] = INFINITY; dk = INFINITY;
+            d = act ? exact_dist(q + qc * dd, rows + (int64_t)ri * dd, dd) : 0.f;
+        }
+        if (!act) continue;
+        // ascending by (distance, index)
+        if (K1) {
+            if (d < bd[0] || (d == bd[0] && ri < bi[0])) { bd[0] = d; bi[0] = ri; }
+        } else {
+            float nd = d;
+            int ni = ri;
+#pragma unroll
+            for (int j = 0; j < RR_K; j++) {
+                const bool sw = nd < bd[j] || (nd == bd[j] && ni < bi[j]);
+                const float td = sw ? bd[j] : nd;
+                const int ti = sw ? bi[j] : ni;
+                bd[j] = sw ? nd : bd[j];
+                bi[j] = sw ? ni : bi[j];
+                nd = td;
+                ni = ti;
+            }
         }
     }
-    // certificate: no row outside the candidate lists can be at or below the k-th exact distance
-    float tau = INFINITY;
-    for (int sp = 0; sp < nsplit; sp++) tau = fminf(tau, cand_tau[qg * nsplit + sp]); // admission threshold at scan end
-    // NaN / overflowed fp16 query operands never certify (their scores are NaN and select nothing)
-    bool ok = qn16[qg] < 3.0e38f;
+    if (!live) return;
+    float dk = 0.f;
+#pragma unroll
+    for (int j = 0; j < (K1 ? 1 : RR_K); j++)
+        if (j < k) {
+            const bool have = bi[j] != 0x7fffffff;
+            idx[qg * k + j] = have ? bi[j] : -1;
+            err[qg * k + j] = have ? bd[j] : INFINITY;
+            dk = have ? bd[j] : INFINITY;
+        }
+    // certificate: no row outside the candidate lists can be at or below the k-th exact distance.
+    // NaN / overflowed fp16 query operands never certify (their scores are NaN and select nothing).
+    bool ok = !overflow && qn16[qg] < 3.0e38f;
     if (ok && tau < INFINITY) {
         const double nsum = (double)qne[qg] + (double)max_tnorm;
         const double a = 6e-5 * nsum * nsum + 1e-6;                   // fp32 accumulation slack
@@ -87,7 +164,7 @@ __global__ void __launch_bounds__(RR_QPB * 8) rerank_kernel(
         double root = sqrt(dt > 0.0 ? dt : 0.0) - e;
         if (root < 0.0) root = 0.0;
         const double lb = root * root * (1.0 - 2e-5);
-        ok = lb > (double)dk && qn16[qg] < 3.0e38f; // NaN / overflowed fp16 operands never certify
+        ok = lb > (double)dk;
     }
     if (!ok) fb_list[atomicAdd(fb_count, 1)] = (int)qg;
 }
@@ -98,10 +175,12 @@ int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, 
                      const int *d_cand_i, const float *d_cand_tau, int nsplit, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
                      float max_tnorm, int k, int *d_idx, float *d_err, int *d_fb_list, int *d_fb_count,
                      cudaStream_t s) {
-    const size_t smem = (size_t)RR_QPB * nsplit * kc * 8;
-    rerank_kernel<<<(unsigned)((nq + RR_QPB - 1) / RR_QPB), RR_QPB * 8, smem, s>>>(
-        d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, max_tnorm, k, d_idx, d_err,
-        d_fb_list, d_fb_count);
+    const unsigned grid = (unsigned)((nq + RR_THREADS - 1) / RR_THREADS);
+    const bool staged = (dd & 3) == 0 && (((uintptr_t)d_q | (uintptr_t)d_rows) & 15) == 0;
+#define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, 0, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, max_tnorm, k, d_idx, d_err, d_fb_list, d_fb_count)
+    if (k == 1) { if (staged) RR_LAUNCH(true, true); else RR_LAUNCH(true, false); }
+    else { if (staged) RR_LAUNCH(false, true); else RR_LAUNCH(false, false); }
+#undef RR_LAUNCH
     tm_count_launch();
     return tm_check(cudaGetLastError(), "rerank_kernel");
 }
