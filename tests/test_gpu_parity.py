@@ -188,6 +188,19 @@ def test_kmodes_assign_bit_exact(tb, oracle, small_case):
         wc, wd = o.kmodes_assign(X, cent, sem)
         assert np.array_equal(clust, wc) and np.array_equal(dis, wd), sem
         assert clust[5] == 500 and dis[5] == 0
+    # nibble fast path and byte path mixed inside one call: narrow rows, one wide centroid in the third
+    # 256-centroid tile, a few wide points in one block; ties between narrow duplicates
+    Xn = rng.integers(0, 16, (3000, 80)).astype(np.uint8)
+    cn = rng.integers(0, 16, (700, 80)).astype(np.uint8)
+    cn[600, 7] = 200
+    cn[650] = cn[10]
+    Xn[40] = cn[10]
+    Xn[1500, 79] = 16
+    for sem in (tb.KM_ASM, tb.KM_GENERIC):
+        clust, dis = tb.kmodes_assign(Xn, cn, sem)
+        wc, wd = o.kmodes_assign(Xn, cn, sem)
+        assert np.array_equal(clust, wc) and np.array_equal(dis, wd), sem
+        assert clust[40] == 650 and dis[40] == 0
     # single centroid, empty inputs
     clust, dis = tb.kmodes_assign(X[:10], cent[:1])
     assert np.all(clust == 0)

@@ -17,7 +17,7 @@
 namespace {
 
 constexpr int KM_WORDS = 20;
-constexpr int KM_TILE = 512; // centroids per shared-memory tile (40 KB)
+constexpr int KM_TILE = 512; // centroids per shared-memory tile (40 KB as byte rows, 24 KB bit-sliced)
 
 __device__ __forceinline__ uint32_t nonzero_bytes(uint32_t d) {
     // 0x80 in every byte of d that is non-zero
@@ -53,12 +53,87 @@ __device__ __forceinline__ uint32_t dissim_words(const uint32_t (&p)[KM_WORDS], 
     return (mism << 11) + sad;
 }
 
+// ---- bit-sliced fast path ---------------------------------------------------------------------
+// With the reference's default palette size (16 colours, main.lfm:452-470) every byte of a row is < 16
+// (64 palette indices + 16 zone flags 0/1).  Such a row is also stored bit-sliced: plane b (b = 0..3)
+// holds bit b of all 80 values in three words.  The mismatch mask of 32 positions is then
+// (a0^c0)|(a1^c1)|(a2^c2)|(a3^c3) = four LOP3, one POPC per 32 positions, i.e. ~17 instructions for the
+// whole mismatch count instead of ~110 on bytes.  The mismatch count dominates the dissimilarity
+// (<< 11), so the byte-wise SAD term is only evaluated (from the L1/L2-resident byte rows) for the
+// few centroids whose mismatch count alone does not already exceed the running best
+// (dis >= mismatches << 11).  Results are bit-identical to the byte path, which is still taken by
+// blocks that see a byte >= 16 in their points or when any centroid has one.
+constexpr int KM_PLANES = 4;
+constexpr int KM_BWORDS = 12; // 4 planes x 3 words
+
+// gather bit b of the 4 bytes of w into bits 0..3 (byte i -> bit i)
+__device__ __forceinline__ uint32_t gather_bit(uint32_t w, int b) {
+    return ((((w >> b) & 0x01010101u) * 0x01020408u) >> 24) & 0xfu;
+}
+// 20 byte words -> 12 bit-sliced words
+__device__ __forceinline__ void bitslice_row(const uint32_t (&p)[KM_WORDS], uint32_t (&out)[KM_BWORDS]) {
+#pragma unroll
+    for (int b = 0; b < KM_PLANES; b++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            uint32_t v = 0;
+#pragma unroll
+            for (int w = 0; w < 8; w++)
+                if (8 * j + w < KM_WORDS) v |= gather_bit(p[8 * j + w], b) << (4 * w);
+            out[b * 3 + j] = v;
+        }
+}
+
+// SAD part of the dissimilarity only (the mismatch count comes from the bit-sliced words)
 template <int SEM>
-__global__ void __launch_bounds__(256) kmodes_assign_kernel(const uint32_t *__restrict__ X, int64_t np,
+__device__ __forceinline__ uint32_t sad_words(const uint32_t (&p)[KM_WORDS], const uint32_t *__restrict__ c) {
+    uint32_t sad = 0;
+    uint32_t cw[KM_WORDS];
+#pragma unroll
+    for (int w = 0; w < KM_WORDS; w += 4) {
+        uint4 v = __ldg(reinterpret_cast<const uint4 *>(c + w));
+        cw[w] = v.x; cw[w + 1] = v.y; cw[w + 2] = v.z; cw[w + 3] = v.w;
+    }
+#pragma unroll
+    for (int w = (SEM == TM_KM_GENERIC ? 0 : 4); w < KM_WORDS; w++) sad = __vsadu4(p[w], cw[w]) + sad;
+    if (SEM == TM_KM_ASM) {
+        sad += pabsb_psubb(cw[0] & 0xff, p[0] & 0xff) + (pabsb_psubb((cw[0] >> 8) & 0xff, (p[0] >> 8) & 0xff) << 8);
+        sad += pabsb_psubb(cw[2] & 0xff, p[2] & 0xff) + (pabsb_psubb((cw[2] >> 8) & 0xff, (p[2] >> 8) & 0xff) << 8);
+    }
+    return sad;
+}
+
+// one thread per centroid: bit-sliced copy + "some byte >= 16" flag
+__global__ void kmodes_pack_centroids_kernel(const uint32_t *__restrict__ C, int64_t k, uint32_t *__restrict__ Cb,
+                                             int *__restrict__ wide_flag) {
+    int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= k) return;
+    uint32_t p[KM_WORDS], wide = 0;
+    const uint4 *src = reinterpret_cast<const uint4 *>(C + c * KM_WORDS);
+#pragma unroll
+    for (int w = 0; w < 5; w++) {
+        uint4 v = __ldg(src + w);
+        p[4 * w] = v.x; p[4 * w + 1] = v.y; p[4 * w + 2] = v.z; p[4 * w + 3] = v.w;
+    }
+#pragma unroll
+    for (int w = 0; w < KM_WORDS; w++) wide |= p[w];
+    if (wide & 0xf0f0f0f0u) atomicOr(wide_flag, 1);
+    uint32_t o[KM_BWORDS];
+    bitslice_row(p, o);
+    uint4 *dst = reinterpret_cast<uint4 *>(Cb + c * KM_BWORDS);
+    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
+    dst[2] = make_uint4(o[8], o[9], o[10], o[11]);
+}
+
+template <int SEM>
+__global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *__restrict__ X, int64_t np,
                                                              const uint32_t *__restrict__ C, int64_t k,
+                                                             const uint32_t *__restrict__ Cb,
+                                                             const int *__restrict__ cent_wide,
                                                              int32_t *__restrict__ clust,
                                                              uint64_t *__restrict__ dis) {
-    __shared__ __align__(16) uint32_t cs[KM_TILE * KM_WORDS];
+    __shared__ __align__(16) uint32_t cs[KM_TILE * KM_WORDS]; // byte rows, or bit-sliced rows (12 words each)
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t p[KM_WORDS];
     if (i < np) {
@@ -72,18 +147,54 @@ __global__ void __launch_bounds__(256) kmodes_assign_kernel(const uint32_t *__re
 #pragma unroll
         for (int w = 0; w < KM_WORDS; w++) p[w] = 0;
     }
+    uint32_t wide = 0;
+#pragma unroll
+    for (int w = 0; w < KM_WORDS; w++) wide |= p[w];
+    const bool fast = !__syncthreads_or((wide & 0xf0f0f0f0u) != 0) && *cent_wide == 0; // block-uniform
     uint32_t best = 0xffffffffu;
     int bi = -1;
-    for (int64_t c0 = 0; c0 < k; c0 += KM_TILE) {
-        int cnt = (int)min((int64_t)KM_TILE, k - c0);
-        __syncthreads();
-        const uint4 *src = reinterpret_cast<const uint4 *>(C + c0 * KM_WORDS);
-        for (int e = threadIdx.x; e < cnt * 5; e += blockDim.x) reinterpret_cast<uint4 *>(cs)[e] = __ldg(src + e);
-        __syncthreads();
+    if (fast) {
+        uint32_t pb[KM_BWORDS];
+        bitslice_row(p, pb);
+        for (int64_t c0 = 0; c0 < k; c0 += KM_TILE) {
+            int cnt = (int)min((int64_t)KM_TILE, k - c0);
+            __syncthreads();
+            const uint4 *src = reinterpret_cast<const uint4 *>(Cb + c0 * KM_BWORDS);
+            for (int e = threadIdx.x; e < cnt * 3; e += blockDim.x) reinterpret_cast<uint4 *>(cs)[e] = __ldg(src + e);
+            __syncthreads();
+#pragma unroll 4
+            for (int c = 0; c < cnt; c++) {
+                const uint4 *cn = reinterpret_cast<const uint4 *>(cs + c * KM_BWORDS);
+                const uint4 v0 = cn[0], v1 = cn[1], v2 = cn[2];
+                const uint32_t cw[KM_BWORDS] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w, v2.x, v2.y, v2.z, v2.w};
+                uint32_t mism = 0;
+#pragma unroll
+                for (int j = 0; j < 3; j++) {
+                    uint32_t m = pb[j] ^ cw[j];
+                    m |= pb[3 + j] ^ cw[3 + j];
+                    m |= pb[6 + j] ^ cw[6 + j];
+                    m |= pb[9 + j] ^ cw[9 + j];
+                    mism += __popc(m);
+                }
+                const uint32_t key = mism << 11;
+                if (key <= best) { // otherwise dis >= key > best: cannot win, cannot tie
+                    const uint32_t d = key + sad_words<SEM>(p, C + (c0 + c) * KM_WORDS);
+                    if (d <= best) { best = d; bi = (int)(c0 + c); } // last index wins ties
+                }
+            }
+        }
+    } else {
+        for (int64_t c0 = 0; c0 < k; c0 += KM_TILE) {
+            int cnt = (int)min((int64_t)KM_TILE, k - c0);
+            __syncthreads();
+            const uint4 *src = reinterpret_cast<const uint4 *>(C + c0 * KM_WORDS);
+            for (int e = threadIdx.x; e < cnt * 5; e += blockDim.x) reinterpret_cast<uint4 *>(cs)[e] = __ldg(src + e);
+            __syncthreads();
 #pragma unroll 2
-        for (int c = 0; c < cnt; c++) {
-            uint32_t d = dissim_words<SEM>(p, cs + c * KM_WORDS);
-            if (d <= best) { best = d; bi = (int)(c0 + c); } // last index wins ties
+            for (int c = 0; c < cnt; c++) {
+                uint32_t d = dissim_words<SEM>(p, cs + c * KM_WORDS);
+                if (d <= best) { best = d; bi = (int)(c0 + c); } // last index wins ties
+            }
         }
     }
     if (i < np) {
@@ -115,16 +226,39 @@ __global__ void kmodes_umd_kernel(const uint32_t *__restrict__ X, int64_t np, co
 
 } // namespace
 
+namespace {
+struct KmScratch { // grow-only: bit-sliced centroids + wide flag
+    uint32_t *cb = nullptr;
+    int *flag = nullptr;
+    size_t cap = 0;
+    std::mutex mu;
+} g_km;
+} // namespace
+
 int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
                             int32_t *d_clust, uint64_t *d_dis, cudaStream_t s) {
     if (sem != TM_KM_ASM && sem != TM_KM_GENERIC) { tm_set_error("unknown KModes semantics %d", sem); return TM_EINVAL; }
     if (np == 0) return 0;
     if (((uintptr_t)d_X & 15) || ((uintptr_t)d_c & 15)) { tm_set_error("KModes rows must be 16-byte aligned"); return TM_EINVAL; }
+    std::lock_guard<std::mutex> lk(g_km.mu);
+    if ((size_t)k > g_km.cap || !g_km.flag) {
+        cudaStreamSynchronize(s);
+        cudaFree(g_km.cb);
+        g_km.cb = nullptr; g_km.cap = 0;
+        TM_CUDA(cudaMalloc(&g_km.cb, sizeof(uint32_t) * KM_BWORDS * (size_t)(k > 0 ? k : 1)));
+        if (!g_km.flag) TM_CUDA(cudaMalloc(&g_km.flag, sizeof(int)));
+        g_km.cap = (size_t)(k > 0 ? k : 1);
+    }
+    TM_CUDA(cudaMemsetAsync(g_km.flag, 0, sizeof(int), s));
+    if (k > 0) {
+        kmodes_pack_centroids_kernel<<<(unsigned)((k + 127) / 128), 128, 0, s>>>((const uint32_t *)d_c, k, g_km.cb, g_km.flag);
+        tm_count_launch();
+    }
     unsigned grid = (unsigned)((np + 255) / 256);
     if (sem == TM_KM_ASM)
-        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, d_clust, d_dis);
+        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis);
     else
-        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, d_clust, d_dis);
+        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "kmodes_assign_kernel");
 }
