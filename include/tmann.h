@@ -132,6 +132,24 @@ TM_API int tm_frametiling_search_dev(ANNkdtree *akd, const int32_t *d_rgb, int64
 TM_API ANNkdtree *tm_global_dataset_create(const uint8_t *h_palpix, int64_t ntiles,
                                            int32_t *h_tr_tile, uint8_t *h_tr_attrs);
 
+/* One-call PrepareFrameTiling (main.pas:3791-3967) for a keyframe.  global_ds is the stage-1 handle
+ * of tm_global_dataset_create over the same ntiles tiles.  h_item_pal / h_item_tile list the
+ * (PalIdx, GlobalTileIndex) of every tilemap position of the keyframe's frames (duplicates allowed, the
+ * "already seen" test of main.pas:3814-3821 is done on the device).  For each distinct pair the 8
+ * nearest stage-1 rows of the tile's line are taken (UseOne main.pas:3830; hits with an err equal to the
+ * previous hit's are skipped, 3835-3837) and used[pal'][tile'][attrs'] is set for pal' = own palette
+ * (quality 0, ftFast), palettes whose centroid distance to the own palette is < pal_tol * max
+ * (quality 1, ftMedium; h_pal_centroids[npal][192] doubles = KF.PaletteCentroids, pal_tol =
+ * cFTPaletteTol 0.05), or all palettes (quality 2, ftSlow).  The used rows are rendered in DoPsyV's
+ * order (pal, tile, vmir, hmir; main.pas:3883-3919) and become the returned stage-2 dataset
+ * (tm_dataset_rows = KNNSize); tm_keyframe_tables copies TRToTileIdx / TRToPalIdx / TRToAttrs. */
+TM_API ANNkdtree *tm_keyframe_dataset_create(ANNkdtree *global_ds, const uint8_t *h_palpix, int64_t ntiles,
+                                             const uint8_t *h_tile_flags, const int32_t *h_pals, int npal,
+                                             int pal_size, const int32_t *h_item_pal, const int32_t *h_item_tile,
+                                             int64_t nitems, int quality, double pal_tol,
+                                             const double *h_pal_centroids, int flags, int gamma);
+TM_API int tm_keyframe_tables(const ANNkdtree *akd, int32_t *h_tr_tile, int32_t *h_tr_pal, uint8_t *h_tr_attrs);
+
 /* KModes assignment pass (DoGMMD kmodes.pas:825-835; loops 866-878, 984-997):
  * clust[i] = arg-min over k centroids of the matching dissimilarity, last index
  * wins ties (kmodes.pas:414-415); dis[i] (may be NULL) = that dissimilarity.

@@ -111,3 +111,91 @@ void tmo_nn1_blocked_f32(const float *data, int64_t n, int dd, const float *q,
         for (int b = 0; b < nb; b++) { idx[q0 + b] = bi[b]; dist[q0 + b] = bd[b]; }
     }
 }
+
+/* ---- PrepareFrameTiling (main.pas:3791-3967) ----------------------------------------------
+ * Stage 1 of a keyframe: which (palette, tile, mirror) rows enter the stage-2 dataset.
+ * For every distinct (PalIdx, GlobalTileIndex) of the keyframe's tilemaps (UseOne, 3802-3853):
+ *   the 8 nearest stage-1 rows of the tile's palette-index line (ann_kdtree_search_multi, 3830);
+ *   hits whose err equals the previous hit's err are skipped (3835-3837);
+ *   used[pal'][TRToTileIdx[idx]][TRToAttrs[idx]] := True for pal' = own palette (ftFast),
+ *   every palette whose centroid distance to the own palette is < APalTol * HighestCorr
+ *   (ftMedium, 3846, Corrs from BuildPaletteCorrTriangle 3855-3867), or all palettes (ftSlow).
+ * ANN's order among equal distances is unspecified (kd-tree traversal); this restatement, like the
+ * CUDA library, lists equal distances by ascending row index.
+ * used: [npal][ntiles][4] indexed by attrs = hmir | vmir << 1.  Returns KNNSize (3942-3950). */
+static double sq_dist_192(const double *a, const double *b) { /* CompareEuclideanDCTPtr main.pas:659-675 */
+    double r = 0;
+    for (int i = 0; i < TMO_DCT_SIZE; i++) { double d = a[i] - b[i]; r += d * d; }
+    return r;
+}
+
+int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int npal,
+                                      const int32_t *item_pal, const int32_t *item_tile, int64_t nitems,
+                                      int quality, double pal_tol, const double *pal_centroids,
+                                      uint8_t *used) {
+    static const uint8_t attrs_of[4] = {0, 1, 3, 2}; /* PrepareGlobalFT row order none,H,HV,V main.pas:3753 */
+    int64_t n = ntiles * 4;
+    float *g = (float *)malloc(sizeof(float) * (size_t)n * 64);
+    tmo_global_rows_f32(palpix, ntiles, g, NULL, NULL);
+    memset(used, 0, (size_t)npal * ntiles * 4);
+    uint8_t *seen = (uint8_t *)calloc((size_t)npal * ntiles, 1);
+    double *corr = NULL, highest = 0.0;
+    if (quality == 1) {
+        corr = (double *)malloc(sizeof(double) * npal * npal);
+        for (int j = 0; j < npal; j++)
+            for (int i = 0; i < npal; i++) {
+                double c = sq_dist_192(pal_centroids + (size_t)j * TMO_DCT_SIZE, pal_centroids + (size_t)i * TMO_DCT_SIZE);
+                corr[j * npal + i] = c;
+                if (!isnan(c) && c > highest) highest = c;
+            }
+    }
+    for (int64_t it = 0; it < nitems; it++) {
+        int pal = item_pal[it];
+        int64_t tile = item_tile[it];
+        if (seen[(size_t)pal * ntiles + tile]) continue;
+        seen[(size_t)pal * ntiles + tile] = 1;
+        int32_t idxs[8];
+        float errs[8];
+        tmo_knn_f32(g, n, 64, g + (size_t)tile * 4 * 64, 1, 8, idxs, errs); /* Line = the stored tile's PalPixels */
+        float last = INFINITY;
+        for (int i = 0; i < 8; i++) {
+            if (idxs[i] < 0) break; /* fewer than 8 rows */
+            if (errs[i] == last) continue;
+            last = errs[i];
+            int64_t t2 = idxs[i] >> 2;
+            int a2 = attrs_of[idxs[i] & 3];
+            for (int p = 0; p < npal; p++) {
+                int on = quality == 0 ? (p == pal)
+                       : quality == 1 ? (corr[p * npal + pal] < pal_tol * highest)
+                                      : 1;
+                if (on) used[((size_t)p * ntiles + t2) * 4 + a2] = 1;
+            }
+        }
+    }
+    int64_t cnt = 0;
+    for (size_t i = 0; i < (size_t)npal * ntiles * 4; i++) cnt += used[i];
+    free(g); free(seen); free(corr);
+    return cnt;
+}
+
+/* DoPsyV main.pas:3883-3919: rows in order pal, tile, vmir, hmir; effective mirror = flag xor tile flag */
+void tmo_frame_tiling_rows(const uint8_t *used, const uint8_t *palpix, int64_t ntiles, const uint8_t *tile_flags,
+                           const int32_t *pals, int npal, int pal_size, int use_wavelets, int gamma,
+                           float *rows, int32_t *tr_tile, int32_t *tr_pal, uint8_t *tr_attrs) {
+    int64_t di = 0;
+    double dct[TMO_DCT_SIZE];
+    for (int p = 0; p < npal; p++)
+        for (int64_t t = 0; t < ntiles; t++)
+            for (int vm = 0; vm < 2; vm++)
+                for (int hm = 0; hm < 2; hm++) {
+                    if (!used[((size_t)p * ntiles + t) * 4 + ((vm << 1) | hm)]) continue;
+                    int fl = tile_flags ? tile_flags[t] : 0;
+                    tmo_psyv(NULL, palpix + t * 64, pals + (size_t)p * pal_size, 1, use_wavelets, 0,
+                             hm ^ (fl & 1), vm ^ ((fl >> 1) & 1), gamma, dct);
+                    for (int j = 0; j < TMO_DCT_SIZE; j++) rows[di * TMO_DCT_SIZE + j] = (float)dct[j];
+                    tr_tile[di] = (int32_t)t;
+                    tr_pal[di] = p;
+                    tr_attrs[di] = (uint8_t)(hm | (vm << 1));
+                    di++;
+                }
+}

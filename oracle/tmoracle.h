@@ -64,6 +64,15 @@ void tmo_knn_f32(const float *data, int64_t n, int dd, const float *q, int64_t n
 /* timed CPU baseline: blocked brute-force 1-NN, float32, OpenMP over queries */
 void tmo_nn1_blocked_f32(const float *data, int64_t n, int dd, const float *q,
                          int64_t nq, int32_t *idx, float *dist, int nthreads);
+/* PrepareFrameTiling main.pas:3791-3967: used[npal][ntiles][4] table (returns KNNSize), then the
+ * stage-2 rows + side tables in DoPsyV order.  quality: 0 ftFast, 1 ftMedium, 2 ftSlow. */
+int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int npal,
+                                      const int32_t *item_pal, const int32_t *item_tile, int64_t nitems,
+                                      int quality, double pal_tol, const double *pal_centroids,
+                                      uint8_t *used);
+void tmo_frame_tiling_rows(const uint8_t *used, const uint8_t *palpix, int64_t ntiles, const uint8_t *tile_flags,
+                           const int32_t *pals, int npal, int pal_size, int use_wavelets, int gamma,
+                           float *rows, int32_t *tr_tile, int32_t *tr_pal, uint8_t *tr_attrs);
 int  tmo_max_threads(void);
 void tmo_set_threads(int n);
 

@@ -166,6 +166,34 @@ def nn1_blocked_f32(data, q, nthreads=0):
     return idx, dist
 
 
+def prepare_frame_tiling(palpix, pals, item_pal, item_tile, quality=1, pal_tol=0.05, pal_centroids=None,
+                         tile_flags=None, use_wavelets=True, gamma=-1):
+    """PrepareFrameTiling (main.pas:3791-3967): returns (rows[KNNSize][192] f32, tr_tile, tr_pal, tr_attrs, used)."""
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    pals = np.ascontiguousarray(pals, np.int32)
+    pals = pals.reshape(1, -1) if pals.ndim == 1 else pals
+    npal, ps = pals.shape
+    nt = palpix.shape[0]
+    item_pal = np.ascontiguousarray(item_pal, np.int32)
+    item_tile = np.ascontiguousarray(item_tile, np.int32)
+    cen = None if pal_centroids is None else np.ascontiguousarray(pal_centroids, np.float64).reshape(npal, 192)
+    tf = None if tile_flags is None else np.ascontiguousarray(tile_flags, np.uint8)
+    used = np.zeros((npal, nt, 4), np.uint8)
+    _lib.tmo_prepare_frame_tiling_used.restype = C.c_int64
+    n = _lib.tmo_prepare_frame_tiling_used(_p(palpix, C.c_uint8), i64(nt), int(npal), _p(item_pal, C.c_int32),
+                                           _p(item_tile, C.c_int32), i64(len(item_pal)), int(quality),
+                                           C.c_double(pal_tol), _p(cen, C.c_double), _p(used, C.c_uint8))
+    rows = np.empty((n, 192), np.float32)
+    tr_tile = np.empty(n, np.int32)
+    tr_pal = np.empty(n, np.int32)
+    tr_attrs = np.empty(n, np.uint8)
+    _lib.tmo_frame_tiling_rows(_p(used, C.c_uint8), _p(palpix, C.c_uint8), i64(nt), _p(tf, C.c_uint8),
+                               _p(pals, C.c_int32), int(npal), int(ps), int(use_wavelets), int(gamma),
+                               _p(rows, C.c_float), _p(tr_tile, C.c_int32), _p(tr_pal, C.c_int32),
+                               _p(tr_attrs, C.c_uint8))
+    return rows, tr_tile, tr_pal, tr_attrs, used
+
+
 class KDTreeRef:
     """ANN-style kd-tree (kdtree_ref.c): ann_kdtree_create(rows, n, dd, 1, ANN_KD_STD) + eps = 0 search."""
 

@@ -261,3 +261,37 @@ def test_kdtree_edge_cases(oracle):
     i, d = one.search(rows[3], 3)
     assert i[0, 0] == 0 and i[0, 1] == -1 and i[0, 2] == -1
     one.close()
+
+
+# ---- PrepareFrameTiling restatement (main.pas:3791-3967): hand-checkable cases
+def test_prepare_frame_tiling_known_cases(oracle):
+    o = oracle
+    pal, s = o.gen_palette(o.BASE_SEED + 3)
+    pals = np.stack([pal, pal[::-1].copy()])
+    tiles = np.zeros((3, 64), np.uint8)
+    tiles[0] = 5                                  # flat tile: its 4 stage-1 rows are identical
+    tiles[1] = np.arange(64) % 16                 # no symmetry
+    tiles[2] = 9                                  # another flat tile, distance 64 * 16 from tile 0
+    # one tilemap item (pal 1, tile 0), ftFast: hits = the 4 identical rows of tile 0 (err 0, only the first kept:
+    # row 0 -> attrs 0), then the 4 identical rows of tile 2 (err 1024, first kept), 8 hits in total
+    rows, tt, tp, ta, used = o.prepare_frame_tiling(tiles, pals, [1], [0], quality=0)
+    assert used[0].sum() == 0                      # ftFast: own palette only (main.pas:3842)
+    assert used[1].tolist() == [[1, 0, 0, 0], [0, 0, 0, 0], [1, 0, 0, 0]]
+    assert tt.tolist() == [0, 2] and tp.tolist() == [1, 1] and ta.tolist() == [0, 0]
+    # rows are the palette-rendered descriptors in DoPsyV order
+    want = o.psyv(palpix=tiles[0], pal=pals[1]).astype(np.float32)
+    assert np.array_equal(rows[0], want)
+    # ftSlow marks every palette (main.pas:3848-3850); duplicates of the item are ignored (3814-3821)
+    rows2, tt2, tp2, ta2, used2 = o.prepare_frame_tiling(tiles, pals, [1, 1, 1], [0, 0, 0], quality=2)
+    assert np.array_equal(used2[0], used2[1]) and used2[0].sum() == 2 and tp2.tolist() == [0, 0, 1, 1]
+    # ftMedium: palette 0 is selected for an item of palette 1 only if their centroid distance < tol * max
+    cen = np.zeros((2, 192))
+    cen[1, 0] = 2.0                                # squared distance 4 = the maximum
+    _, _, tpm, _, um = o.prepare_frame_tiling(tiles, pals, [1], [0], quality=1, pal_tol=0.05, pal_centroids=cen)
+    assert um[0].sum() == 0 and um[1].sum() == 2   # 4 < 0.05 * 4 is false; own palette: 0 < 0.2 is true
+    _, _, _, _, um2 = o.prepare_frame_tiling(tiles, pals, [1], [0], quality=1, pal_tol=1.5, pal_centroids=cen)
+    assert um2[0].sum() == 2
+    # tile flags flip the rendered orientation, not the attrs (main.pas:3910-3912)
+    r3, t3, _, a3, _ = o.prepare_frame_tiling(tiles, pals, [0], [1], quality=0, tile_flags=[0, 1, 0])
+    i = int(np.where((a3 == 0) & (t3 == 1))[0][0])
+    assert np.array_equal(r3[i], o.psyv(palpix=tiles[1], pal=pals[0], hmirror=True).astype(np.float32))

@@ -54,6 +54,8 @@ PROTOTYPES = {
     "tm_frametiling_search": (i32, [vp, vp, i64, i32, i32, vp, vp]),
     "tm_frametiling_search_dev": (i32, [vp, vp, i64, i32, i32, vp, vp]),
     "tm_global_dataset_create": (vp, [vp, i64, vp, vp]),
+    "tm_keyframe_dataset_create": (vp, [vp, vp, i64, vp, vp, i32, i32, vp, vp, i64, i32, C.c_double, vp, i32, i32]),
+    "tm_keyframe_tables": (i32, [vp, vp, vp, vp]),
     "tm_kmodes_assign": (i32, [vp, i64, vp, i64, i32, vp, vp]),
     "tm_kmodes_assign_dev": (i32, [vp, i64, vp, i64, i32, vp, vp]),
     "tm_kmodes_update_min_distance": (i32, [vp, i64, vp, i32, vp]),

@@ -106,6 +106,28 @@ class KDTree:
         h = lib.tm_global_dataset_create(_hp(palpix), palpix.shape[0], _hp(tr_tile), _hp(tr_attrs))
         return cls(h), tr_tile, tr_attrs
 
+    def keyframe_dataset(self, palpix, pals, item_pal, item_tile, quality=1, pal_tol=0.05, pal_centroids=None,
+                         tile_flags=None, wavelets=True, gamma=-1):
+        """PrepareFrameTiling (main.pas:3791-3967) in one call; self is the stage-1 tree of global_ft().
+        Returns the stage-2 tree; its .attrs holds TRToTileIdx / TRToPalIdx / TRToAttrs."""
+        palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+        pals = np.ascontiguousarray(pals, np.int32)
+        pals = pals.reshape(1, -1) if pals.ndim == 1 else pals
+        item_pal = np.ascontiguousarray(item_pal, np.int32)
+        item_tile = np.ascontiguousarray(item_tile, np.int32)
+        cen = None if pal_centroids is None else np.ascontiguousarray(pal_centroids, np.float64)
+        tf = None if tile_flags is None else np.ascontiguousarray(tile_flags, np.uint8)
+        flags = PSYV_WAVELETS if wavelets else 0
+        h = lib.tm_keyframe_dataset_create(self._h, _hp(palpix), palpix.shape[0], _hp(tf), _hp(pals), pals.shape[0],
+                                           pals.shape[1], _hp(item_pal), _hp(item_tile), len(item_pal), int(quality),
+                                           float(pal_tol), _hp(cen), flags, gamma)
+        t = KDTree(h)
+        n = t.n
+        tr_tile, tr_pal, tr_attrs = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.uint8)
+        check(lib.tm_keyframe_tables(t._h, _hp(tr_tile), _hp(tr_pal), _hp(tr_attrs)))
+        t.attrs = dict(tr_tile=tr_tile, tr_pal=tr_pal, tr_attrs=tr_attrs)
+        return t
+
     # -- lifetime ---------------------------------------------------------------
     def destroy(self):
         if self._h:

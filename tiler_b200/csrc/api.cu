@@ -177,6 +177,8 @@ static void free_handle(ANNkdtree *h) {
     if (!h) return;
     cudaFree(h->rows_f32); cudaFree(h->rows_f16); cudaFree(h->norms); cudaFree(h->norm_tiles); cudaFree(h->mean);
     cudaFree(h->d_q1); cudaFree(h->d_i1); cudaFree(h->d_e1);
+    cudaFree(h->knn8_idx); cudaFree(h->knn8_err);
+    free(h->h_tr_tile); free(h->h_tr_pal); free(h->h_tr_attrs);
     if (h->h_pin) cudaFreeHost(h->h_pin);
     free(h->tmap_rows);
     delete h->single_mu;
@@ -363,3 +365,4 @@ int tm_set_profiling(int on) {
 } // extern "C"
 
 #include "api_fused.inc"
+#include "api_keyframe.inc"

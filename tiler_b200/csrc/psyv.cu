@@ -173,15 +173,17 @@ __global__ void __launch_bounds__(192) psyv_tileset_kernel(const uint8_t *__rest
                                                             const PsyvTables *__restrict__ tabs, PsyvConsts K,
                                                             const double *__restrict__ lut,
                                                             const double *__restrict__ qw,
+                                                            const int64_t *__restrict__ row_map, int64_t nrows,
                                                             float *__restrict__ out) {
     __shared__ PsyvTables T;
     for (int i = threadIdx.x; i < (int)(sizeof(PsyvTables) / 8); i += blockDim.x)
         reinterpret_cast<double *>(&T)[i] = reinterpret_cast<const double *>(tabs)[i];
     __syncthreads();
     int plane = threadIdx.x / 64;
-    int64_t row = (int64_t)blockIdx.x * 64 + (threadIdx.x & 63);
-    int64_t nrows = ntiles * 4 * npal;
-    if (row >= nrows) return;
+    const int64_t orow = (int64_t)blockIdx.x * 64 + (threadIdx.x & 63); // output row
+    if (orow >= nrows) return;
+    // source (pal, tile, vmir, hmir): every combination in order, or the keyframe's used subset
+    const int64_t row = row_map ? row_map[orow] : orow;
     int hmir = (int)(row & 1), vmir = (int)((row >> 1) & 1);
     int64_t t = (row >> 2) % ntiles;
     int p = (int)((row >> 2) / ntiles);
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(192) psyv_tileset_kernel(const uint8_t *__rest
             int pi = (wn >> sh) & 0xff;
             a[y * 8 + x] = plane_value(__ldg(pal + pi), plane, &T, K);
         }
-    float *dst = out + row * TM_DCT + plane * 64;
+    float *dst = out + orow * TM_DCT + plane * 64;
     if (WAVELETS) {
         haar_level<8>(a, K.haar);
         haar_level<4>(a, K.haar);
@@ -340,11 +342,10 @@ int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamm
     return tm_check(cudaGetLastError(), "psyv_queries_kernel");
 }
 
-int tm_launch_psyv_tileset(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal,
-                           int pal_size, const uint8_t *d_tile_flags, int flags, int gamma,
-                           float *d_out, cudaStream_t s) {
+int tm_launch_psyv_tileset_rows(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal,
+                                int pal_size, const uint8_t *d_tile_flags, int flags, int gamma,
+                                const int64_t *d_row_map, int64_t nrows, float *d_out, cudaStream_t s) {
     if (gamma < -1 || gamma > 1) { tm_set_error("gamma must be -1, 0 or 1"); return TM_EINVAL; }
-    int64_t nrows = ntiles * 4 * npal;
     if (nrows == 0) return 0;
     int r = ensure_tables();
     if (r) return r;
@@ -353,12 +354,19 @@ int tm_launch_psyv_tileset(const uint8_t *d_palpix, int64_t ntiles, const int32_
     const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
     if (flags & TM_PSYV_WAVELETS)
         psyv_tileset_kernel<true><<<grid, 192, 0, s>>>(d_palpix, ntiles, d_pals, npal, pal_size, d_tile_flags,
-                                                       g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+                                                       g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_row_map, nrows, d_out);
     else
         psyv_tileset_kernel<false><<<grid, 192, 0, s>>>(d_palpix, ntiles, d_pals, npal, pal_size, d_tile_flags,
-                                                        g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+                                                        g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_row_map, nrows, d_out);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "psyv_tileset_kernel");
+}
+
+int tm_launch_psyv_tileset(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal,
+                           int pal_size, const uint8_t *d_tile_flags, int flags, int gamma,
+                           float *d_out, cudaStream_t s) {
+    return tm_launch_psyv_tileset_rows(d_palpix, ntiles, d_pals, npal, pal_size, d_tile_flags, flags, gamma, nullptr,
+                                       ntiles * 4 * npal, d_out, s);
 }
 
 int tm_launch_global_rows(const uint8_t *d_palpix, int64_t ntiles, float *d_out, cudaStream_t s) {

@@ -37,6 +37,12 @@ struct ANNkdtree {
     float *d_q1;
     int *d_i1;
     float *d_e1;
+    // stage-1 (global, dd = 64) datasets: cached 8-NN of every stored tile's own line (UseOne main.pas:3830)
+    int *knn8_idx;
+    float *knn8_err;
+    // keyframe (stage-2) datasets built by tm_keyframe_dataset_create: row -> (tile, pal, attrs) side tables
+    int32_t *h_tr_tile, *h_tr_pal;
+    uint8_t *h_tr_attrs;
 };
 #define TM_MAGIC 0x544d414eu
 
@@ -65,6 +71,19 @@ int tm_launch_psyv_tileset(const uint8_t *d_palpix, int64_t ntiles, const int32_
                            int pal_size, const uint8_t *d_tile_flags, int flags, int gamma,
                            float *d_out, cudaStream_t s);
 int tm_launch_global_rows(const uint8_t *d_palpix, int64_t ntiles, float *d_out, cudaStream_t s);
+// tileset rows for an explicit row list: d_row_map[r] = ((pal * ntiles + tile) * 2 + vmir) * 2 + hmir
+int tm_launch_psyv_tileset_rows(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal,
+                                int pal_size, const uint8_t *d_tile_flags, int flags, int gamma,
+                                const int64_t *d_row_map, int64_t nrows, float *d_out, cudaStream_t s);
+
+// ---- keyframe preparation (keyframe.cu): PrepareFrameTiling main.pas:3791-3967 on the device
+int tm_launch_kf_mark(const int32_t *d_item_pal, const int32_t *d_item_tile, int64_t nitems, int64_t ntiles, int npal,
+                      const int *d_knn_idx, const float *d_knn_err, const uint8_t *d_palmask, uint32_t *d_seen,
+                      uint8_t *d_used, int *d_bad, cudaStream_t s);
+// stream compaction of used[] in index order; *h_count = KNNSize (synchronises s)
+int tm_kf_compact(const uint8_t *d_used, int64_t n, int64_t **d_row_map_out, int64_t *h_count, cudaStream_t s);
+int tm_launch_kf_tables(const int64_t *d_row_map, int64_t nrows, int64_t ntiles, int32_t *d_tr_tile, int32_t *d_tr_pal,
+                        uint8_t *d_tr_attrs, cudaStream_t s);
 
 // ---- dataset preparation (prep.cu): mean, centred fp16 operand, norms
 int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s);
