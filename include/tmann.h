@@ -163,6 +163,19 @@ TM_API int tm_kmodes_update_min_distance(const uint8_t *h_X, int64_t npoints,
                                          const uint8_t *h_center, int semantics,
                                          uint64_t *h_mindist);
 
+/* InitFarthestFirst (kmodes.pas:698-776) on the device: centroid 0 = X[init_point]; centroid c = the
+ * LAST unused point whose minimum dissimilarity to the chosen ones is largest (`>=`, 765-770).
+ * h_centroids[k][80] out, h_chosen[k] (may be NULL) = the chosen point indices.  k <= npoints. */
+TM_API int tm_kmodes_farthest_first(const uint8_t *h_X, int64_t npoints, int64_t k, int64_t init_point,
+                                    int semantics, uint8_t *h_centroids, int64_t *h_chosen);
+/* Cluster representatives (DoKModes main.pas:4231-4253): h_rep[j] = index of the member of cluster j
+ * (h_labels[i] == j, point order) with the smallest dissimilarity to h_centroids[j], last member among
+ * equals (GetMinMatchingDissim kmodes.pas:414-415); -1 for an empty cluster.  h_count[j] (may be NULL)
+ * = member count (the reference merges only clusters with >= 2 members, main.pas:4247). */
+TM_API int tm_kmodes_representatives(const uint8_t *h_X, int64_t npoints, const int32_t *h_labels,
+                                     const uint8_t *h_centroids, int64_t k, int semantics, int32_t *h_rep,
+                                     int32_t *h_count);
+
 /* counters since the last reset: kernel launches issued by this library, queries
  * that took the exact-fallback path after the tensor-core pass, and the device
  * time (ms, CUDA events) of the last search call split by phase. */

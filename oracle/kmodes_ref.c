@@ -115,3 +115,22 @@ int tmo_kmodes_row(const uint8_t *palpix, int pal_size, uint8_t *row) {
     }
     return res;
 }
+
+/* Per-cluster representative of DoKModes main.pas:4231-4253: for cluster j the members are gathered in
+ * point order (4235-4243) and GetMinMatchingDissim(members, centroid j) picks the nearest, last among
+ * equals.  rep[j] = point index or -1 (empty cluster); count[j] = members. */
+void tmo_kmodes_representatives(const uint8_t *X, int64_t npoints, const int32_t *labels,
+                                const uint8_t *centroids, int64_t k, int semantics, int32_t *rep, int32_t *count) {
+    for (int64_t j = 0; j < k; j++) {
+        uint64_t best = ~(uint64_t)0;
+        int32_t bi = -1, cnt = 0;
+        for (int64_t i = 0; i < npoints; i++) {
+            if (labels[i] != j) continue;
+            cnt++;
+            uint64_t d = tmo_dissim(centroids + j * TMO_KM_FEATURES, X + i * TMO_KM_FEATURES, semantics);
+            if (d <= best) { best = d; bi = (int32_t)i; }
+        }
+        rep[j] = bi;
+        if (count) count[j] = cnt;
+    }
+}

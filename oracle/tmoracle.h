@@ -102,6 +102,9 @@ void tmo_update_min_distance(const uint8_t *X, int64_t npoints, const uint8_t *c
 /* InitFarthestFirst kmodes.pas:698-776 */
 void tmo_farthest_first(const uint8_t *X, int64_t npoints, int64_t k, int64_t init_point,
                         int semantics, uint8_t *centroids, int64_t *chosen);
+/* representative pick of DoKModes main.pas:4231-4253 */
+void tmo_kmodes_representatives(const uint8_t *X, int64_t npoints, const int32_t *labels,
+                                const uint8_t *centroids, int64_t k, int semantics, int32_t *rep, int32_t *count);
 /* WriteTileDatasetLine main.pas:4167-4183 + GetTilePalZoneThres 4142-4165 */
 int  tmo_kmodes_row(const uint8_t *palpix, int pal_size, uint8_t *row80);
 

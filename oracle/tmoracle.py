@@ -270,6 +270,18 @@ def farthest_first(X, k, init_point, semantics=ASM):
     return cent, chosen
 
 
+def kmodes_representatives(X, labels, centroids, semantics=ASM):
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    labels = np.ascontiguousarray(labels, np.int32)
+    centroids = np.ascontiguousarray(centroids, np.uint8).reshape(-1, 80)
+    k = centroids.shape[0]
+    rep = np.empty(k, np.int32)
+    cnt = np.empty(k, np.int32)
+    _lib.tmo_kmodes_representatives(_p(X, C.c_uint8), i64(X.shape[0]), _p(labels, C.c_int32), _p(centroids, C.c_uint8),
+                                    i64(k), int(semantics), _p(rep, C.c_int32), _p(cnt, C.c_int32))
+    return rep, cnt
+
+
 def kmodes_row(palpix, pal_size=16):
     palpix = np.ascontiguousarray(palpix, np.uint8).reshape(64)
     row = np.empty(80, np.uint8)

@@ -219,6 +219,37 @@ def test_kmodes_update_min_distance(tb, oracle):
         assert np.array_equal(got, oracle.update_min_distance(X, X[17], md, sem))
 
 
+def test_kmodes_farthest_first_and_representatives(tb, oracle):
+    o = oracle
+    tiles, _ = o.gen_tileset(o.BASE_SEED + 31, 3000)
+    X = o.kmodes_rows(tiles)
+    X[100] = X[7]      # duplicate rows: ties in the arg-max (last index wins, kmodes.pas:765-770)
+    X[2999] = X[7]
+    for sem in (tb.KM_ASM, tb.KM_GENERIC):
+        cent, chosen = tb.kmodes_farthest_first(X, 40, 17, sem)
+        wc, wch = o.farthest_first(X, 40, 17, sem)
+        assert np.array_equal(chosen, wch) and np.array_equal(cent, wc), sem
+        labels, _ = tb.kmodes_assign(X, cent, sem)
+        rep, cnt = tb.kmodes_representatives(X, labels, cent, sem)
+        wr, wn = o.kmodes_representatives(X, labels, cent, sem)
+        assert np.array_equal(rep, wr) and np.array_equal(cnt, wn), sem
+    # arbitrary bytes, k = npoints (every point chosen exactly once), empty cluster
+    rng = np.random.default_rng(8)
+    Xr = rng.integers(0, 256, (50, 80)).astype(np.uint8)
+    cent, chosen = tb.kmodes_farthest_first(Xr, 50, 0)
+    wc, wch = o.farthest_first(Xr, 50, 0)
+    assert np.array_equal(chosen, wch) and sorted(chosen.tolist()) == list(range(50))
+    lab = np.zeros(50, np.int32)
+    rep, cnt = tb.kmodes_representatives(Xr, lab, Xr[:3])
+    wr, wn = o.kmodes_representatives(Xr, lab, Xr[:3])
+    assert np.array_equal(rep, wr) and rep[1] == -1 and cnt.tolist() == [50, 0, 0]
+    from tiler_b200._lib import TMError
+    with pytest.raises(TMError):
+        tb.kmodes_farthest_first(Xr, 51, 0)
+    with pytest.raises(TMError):
+        tb.kmodes_representatives(Xr, lab + 5, Xr[:3])
+
+
 def test_device_pointer_entry_points(tb, oracle, small_case):
     import torch
     ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])

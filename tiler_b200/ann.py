@@ -232,3 +232,24 @@ def kmodes_update_min_distance(X, center, mindist, semantics=KM_ASM):
     mindist = np.ascontiguousarray(mindist, np.uint64).copy()
     check(lib.tm_kmodes_update_min_distance(_hp(X), X.shape[0], _hp(center), semantics, _hp(mindist)))
     return mindist
+
+
+def kmodes_farthest_first(X, k, init_point, semantics=KM_ASM):
+    """TKModes.InitFarthestFirst (kmodes.pas:698-776): returns (centroids[k][80], chosen[k])."""
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    cent = np.empty((k, 80), np.uint8)
+    chosen = np.empty(k, np.int64)
+    check(lib.tm_kmodes_farthest_first(_hp(X), X.shape[0], int(k), int(init_point), semantics, _hp(cent), _hp(chosen)))
+    return cent, chosen
+
+
+def kmodes_representatives(X, labels, centroids, semantics=KM_ASM):
+    """Per-cluster representative pick of DoKModes (main.pas:4231-4253): returns (rep[k], count[k])."""
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    labels = np.ascontiguousarray(labels, np.int32)
+    centroids = np.ascontiguousarray(centroids, np.uint8).reshape(-1, 80)
+    k = centroids.shape[0]
+    rep = np.empty(k, np.int32)
+    cnt = np.empty(k, np.int32)
+    check(lib.tm_kmodes_representatives(_hp(X), X.shape[0], _hp(labels), _hp(centroids), k, semantics, _hp(rep), _hp(cnt)))
+    return rep, cnt

@@ -224,6 +224,96 @@ __global__ void kmodes_umd_kernel(const uint32_t *__restrict__ X, int64_t np, co
     if (d < m) mind[i] = d; // strict: cmovb kmodes.pas:555-558
 }
 
+// ---- farthest-first initialisation (InitFarthestFirst kmodes.pas:698-776) ------------------------
+// One launch per centroid, no host round trip in between: pass c reads the point chosen by pass c-1
+// from argkey[c] (device memory), records it (chosen[c], centroids[c] = X[cur], used[cur] = 1), folds
+// dissim(X[cur], X[i]) into mindist[i] for EVERY point (the asm's `used` test never skips,
+// kmodes.pas:567) with a strict < (555-558), and reduces the next farthest point: the LAST index among
+// the unused points with the largest mindist (`>=`, 765-770) = the maximum of (mindist << 32 | i).
+// Keys are stored + 1 so that 0 means "no unused point left".  X (80 B / point) stays L2-resident.
+template <int SEM>
+__global__ void __launch_bounds__(256) kmodes_ff_pass_kernel(const uint32_t *__restrict__ X, int64_t np, int c,
+                                                              unsigned long long *__restrict__ argkey,
+                                                              uint32_t *__restrict__ mind, uint8_t *__restrict__ used,
+                                                              uint32_t *__restrict__ cent_out, int64_t *__restrict__ chosen,
+                                                              int *__restrict__ err) {
+    __shared__ __align__(16) uint32_t cs[KM_WORDS];
+    __shared__ unsigned long long wbest[8];
+    const unsigned long long ck = argkey[c];
+    if (ck == 0) { // more centroids requested than points: the reference would index X[-1]
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(err, 1);
+        return;
+    }
+    const uint32_t cur = (uint32_t)((ck - 1) & 0xffffffffull);
+    if (threadIdx.x < KM_WORDS) {
+        const uint32_t w = X[(int64_t)cur * KM_WORDS + threadIdx.x];
+        cs[threadIdx.x] = w;
+        if (blockIdx.x == 0) cent_out[(int64_t)c * KM_WORDS + threadIdx.x] = w;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) { chosen[c] = cur; used[cur] = 1; }
+    __syncthreads();
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long key = 0;
+    if (i < np) {
+        uint32_t p[KM_WORDS];
+        const uint4 *src = reinterpret_cast<const uint4 *>(X + i * KM_WORDS);
+#pragma unroll
+        for (int w = 0; w < 5; w++) {
+            uint4 v = __ldg(src + w);
+            p[4 * w] = v.x; p[4 * w + 1] = v.y; p[4 * w + 2] = v.z; p[4 * w + 3] = v.w;
+        }
+        const uint32_t d = dissim_words<SEM>(p, cs);
+        uint32_t m = mind[i];
+        if (d < m) { m = d; mind[i] = d; }
+        if (i != cur && !used[i]) key = (((unsigned long long)m << 32) | (unsigned long long)i) + 1;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+        key = other > key ? other : key;
+    }
+    if ((threadIdx.x & 31) == 0) wbest[threadIdx.x >> 5] = key;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long b = wbest[0];
+#pragma unroll
+        for (int w = 1; w < 8; w++) b = wbest[w] > b ? wbest[w] : b;
+        if (b) atomicMax(argkey + c + 1, b);
+    }
+}
+
+// ---- cluster representatives (DoKModes main.pas:4231-4253) ----------------------------------------
+// rep[j] = GetMinMatchingDissim(members of cluster j in point order, centroid j): minimum dissimilarity,
+// LAST member among equals (kmodes.pas:414-415) = the minimum of (dis << 32 | ~i).
+template <int SEM>
+__global__ void __launch_bounds__(256) kmodes_rep_kernel(const uint32_t *__restrict__ X, int64_t np,
+                                                          const int32_t *__restrict__ labels,
+                                                          const uint32_t *__restrict__ C, int64_t k,
+                                                          unsigned long long *__restrict__ best, int32_t *__restrict__ count,
+                                                          int *__restrict__ err) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np) return;
+    const int32_t l = labels[i];
+    if (l < 0 || l >= k) { atomicOr(err, 1); return; }
+    uint32_t p[KM_WORDS];
+    const uint4 *src = reinterpret_cast<const uint4 *>(X + i * KM_WORDS);
+#pragma unroll
+    for (int w = 0; w < 5; w++) {
+        uint4 v = __ldg(src + w);
+        p[4 * w] = v.x; p[4 * w + 1] = v.y; p[4 * w + 2] = v.z; p[4 * w + 3] = v.w;
+    }
+    const uint32_t d = dissim_words<SEM>(p, C + (int64_t)l * KM_WORDS);
+    atomicMin(best + l, ((unsigned long long)d << 32) | (unsigned long long)(0xffffffffu - (uint32_t)i));
+    atomicAdd(count + l, 1);
+}
+
+__global__ void kmodes_rep_finish_kernel(const unsigned long long *__restrict__ best, int64_t k, int32_t *__restrict__ rep) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= k) return;
+    const unsigned long long b = best[j];
+    rep[j] = b == ~0ull ? -1 : (int32_t)(0xffffffffu - (uint32_t)(b & 0xffffffffull));
+}
+
 } // namespace
 
 namespace {
@@ -274,4 +364,50 @@ int tm_launch_kmodes_umd(const uint8_t *d_X, int64_t np, const uint8_t *d_center
         kmodes_umd_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_center, d_mind);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "kmodes_umd_kernel");
+}
+
+int tm_launch_kmodes_farthest_first(const uint8_t *d_X, int64_t np, int64_t k, int64_t init_point, int sem,
+                                    uint8_t *d_centroids, int64_t *d_chosen, unsigned long long *d_argkey,
+                                    uint32_t *d_mind, uint8_t *d_used, int *d_err, cudaStream_t s) {
+    if (sem != TM_KM_ASM && sem != TM_KM_GENERIC) { tm_set_error("unknown KModes semantics %d", sem); return TM_EINVAL; }
+    if (k == 0) return 0;
+    TM_CUDA(cudaMemsetAsync(d_argkey, 0, sizeof(unsigned long long) * (size_t)(k + 1), s));
+    TM_CUDA(cudaMemsetAsync(d_mind, 0xff, sizeof(uint32_t) * (size_t)np, s));
+    TM_CUDA(cudaMemsetAsync(d_used, 0, (size_t)np, s));
+    TM_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int), s));
+    const unsigned long long k0 = (unsigned long long)init_point + 1; // (mindist 0, index) + 1
+    TM_CUDA(cudaMemcpyAsync(d_argkey, &k0, sizeof k0, cudaMemcpyHostToDevice, s));
+    TM_CUDA(cudaStreamSynchronize(s)); // k0 is a stack variable
+    const unsigned grid = (unsigned)((np + 255) / 256);
+    for (int64_t c = 0; c < k; c++) {
+        if (sem == TM_KM_ASM)
+            kmodes_ff_pass_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (int)c, d_argkey, d_mind, d_used,
+                                                                 (uint32_t *)d_centroids, d_chosen, d_err);
+        else
+            kmodes_ff_pass_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (int)c, d_argkey, d_mind, d_used,
+                                                                     (uint32_t *)d_centroids, d_chosen, d_err);
+    }
+    tm_count_launch((int)k);
+    return tm_check(cudaGetLastError(), "kmodes_ff_pass_kernel");
+}
+
+int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32_t *d_labels, const uint8_t *d_c, int64_t k,
+                                     int sem, unsigned long long *d_best, int32_t *d_rep, int32_t *d_count, int *d_err,
+                                     cudaStream_t s) {
+    if (sem != TM_KM_ASM && sem != TM_KM_GENERIC) { tm_set_error("unknown KModes semantics %d", sem); return TM_EINVAL; }
+    if (k == 0) return 0;
+    TM_CUDA(cudaMemsetAsync(d_best, 0xff, sizeof(unsigned long long) * (size_t)k, s));
+    TM_CUDA(cudaMemsetAsync(d_count, 0, sizeof(int32_t) * (size_t)k, s));
+    TM_CUDA(cudaMemsetAsync(d_err, 0, sizeof(int), s));
+    if (np) {
+        const unsigned grid = (unsigned)((np + 255) / 256);
+        if (sem == TM_KM_ASM)
+            kmodes_rep_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, d_labels, (const uint32_t *)d_c, k, d_best, d_count, d_err);
+        else
+            kmodes_rep_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, d_labels, (const uint32_t *)d_c, k, d_best, d_count, d_err);
+        tm_count_launch();
+    }
+    kmodes_rep_finish_kernel<<<(unsigned)((k + 255) / 256), 256, 0, s>>>(d_best, k, d_rep);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "kmodes_rep_kernel");
 }

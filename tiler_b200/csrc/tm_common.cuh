@@ -100,5 +100,11 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
 // ---- kmodes (kmodes.cu)
 int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
                             int32_t *d_clust, uint64_t *d_dis, cudaStream_t s);
+int tm_launch_kmodes_farthest_first(const uint8_t *d_X, int64_t np, int64_t k, int64_t init_point, int sem,
+                                    uint8_t *d_centroids, int64_t *d_chosen, unsigned long long *d_argkey,
+                                    uint32_t *d_mind, uint8_t *d_used, int *d_err, cudaStream_t s);
+int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32_t *d_labels, const uint8_t *d_c, int64_t k,
+                                     int sem, unsigned long long *d_best, int32_t *d_rep, int32_t *d_count, int *d_err,
+                                     cudaStream_t s);
 int tm_launch_kmodes_umd(const uint8_t *d_X, int64_t np, const uint8_t *d_center, int sem,
                          uint64_t *d_mind, cudaStream_t s);
