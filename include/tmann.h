@@ -176,6 +176,17 @@ TM_API int tm_kmodes_representatives(const uint8_t *h_X, int64_t npoints, const 
                                      const uint8_t *h_centroids, int64_t k, int semantics, int32_t *h_rep,
                                      int32_t *h_count);
 
+/* Reindex, the consumer of FrameTiling's output (btnReindexClick main.pas:1199-1230 + ReindexTiles
+ * 4483-4527).  tilemap[nitems] = GlobalTileIndex of every tilemap item, rewritten in place to the new
+ * indices.  use_count[ntiles] = UseCount per old tile; idx_map[ntiles] = old -> new index (-1 = inactive,
+ * the $ffffffff of main.pas:4510); order[ntiles] = new -> old for the first *h_active entries (-1 after):
+ * active tiles by UseCount descending, then old index ascending (CompareTileUseCountRev 4472-4481).
+ * The output arrays may be NULL in the host variant. */
+TM_API int tm_reindex(int32_t *h_tilemap, int64_t nitems, int64_t ntiles, int32_t *h_use_count,
+                      int32_t *h_idx_map, int32_t *h_order, int64_t *h_active);
+TM_API int tm_reindex_dev(int32_t *d_tilemap, int64_t nitems, int64_t ntiles, int32_t *d_use_count,
+                          int32_t *d_idx_map, int32_t *d_order, int64_t *h_active);
+
 /* counters since the last reset: kernel launches issued by this library, queries
  * that took the exact-fallback path after the tensor-core pass, and the device
  * time (ms, CUDA events) of the last search call split by phase. */

@@ -199,3 +199,26 @@ void tmo_frame_tiling_rows(const uint8_t *used, const uint8_t *palpix, int64_t n
                     di++;
                 }
 }
+
+/* ---- Reindex: btnReindexClick main.pas:1199-1230 + ReindexTiles 4483-4527 ------------------------ */
+typedef struct { int32_t use, tmp; } ri_tile;
+static int ri_cmp(const void *a, const void *b) { /* CompareTileUseCountRev main.pas:4472-4481 */
+    const ri_tile *x = (const ri_tile *)a, *y = (const ri_tile *)b;
+    if (x->use != y->use) return y->use > x->use ? 1 : -1;
+    return (x->tmp > y->tmp) - (x->tmp < y->tmp);
+}
+int64_t tmo_reindex(int32_t *tilemap, int64_t nitems, int64_t ntiles, int32_t *use_count, int32_t *idx_map,
+                    int32_t *order) {
+    for (int64_t t = 0; t < ntiles; t++) use_count[t] = 0;
+    for (int64_t i = 0; i < nitems; i++) use_count[tilemap[i]]++;           /* 1214-1221 */
+    ri_tile *act = (ri_tile *)malloc(sizeof(ri_tile) * (size_t)(ntiles ? ntiles : 1));
+    int64_t cnt = 0;
+    for (int64_t t = 0; t < ntiles; t++)                                     /* pack, 4497-4507 */
+        if (use_count[t] > 0) { act[cnt].use = use_count[t]; act[cnt].tmp = (int32_t)t; cnt++; }
+    qsort(act, (size_t)cnt, sizeof(ri_tile), ri_cmp);                        /* 4516 */
+    for (int64_t t = 0; t < ntiles; t++) { idx_map[t] = -1; order[t] = -1; } /* 4510 */
+    for (int64_t r = 0; r < cnt; r++) { idx_map[act[r].tmp] = (int32_t)r; order[r] = act[r].tmp; }
+    for (int64_t i = 0; i < nitems; i++) tilemap[i] = idx_map[tilemap[i]];   /* 4523-4526 */
+    free(act);
+    return cnt;
+}

@@ -73,6 +73,9 @@ int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int
 void tmo_frame_tiling_rows(const uint8_t *used, const uint8_t *palpix, int64_t ntiles, const uint8_t *tile_flags,
                            const int32_t *pals, int npal, int pal_size, int use_wavelets, int gamma,
                            float *rows, int32_t *tr_tile, int32_t *tr_pal, uint8_t *tr_attrs);
+/* Reindex main.pas:1199-1230, 4483-4527: rewrites tilemap in place, returns the active tile count */
+int64_t tmo_reindex(int32_t *tilemap, int64_t nitems, int64_t ntiles, int32_t *use_count, int32_t *idx_map,
+                    int32_t *order);
 int  tmo_max_threads(void);
 void tmo_set_threads(int n);
 

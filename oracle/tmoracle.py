@@ -194,6 +194,18 @@ def prepare_frame_tiling(palpix, pals, item_pal, item_tile, quality=1, pal_tol=0
     return rows, tr_tile, tr_pal, tr_attrs, used
 
 
+def reindex(tilemap, ntiles):
+    """btnReindexClick + ReindexTiles: returns (new_tilemap, use_count, idx_map, order[:n_active])."""
+    tm = np.ascontiguousarray(tilemap, np.int32).copy()
+    cnt = np.empty(ntiles, np.int32)
+    imap = np.empty(ntiles, np.int32)
+    order = np.empty(ntiles, np.int32)
+    _lib.tmo_reindex.restype = C.c_int64
+    n = _lib.tmo_reindex(_p(tm, C.c_int32), i64(tm.size), i64(ntiles), _p(cnt, C.c_int32), _p(imap, C.c_int32),
+                         _p(order, C.c_int32))
+    return tm, cnt, imap, order[:n]
+
+
 class KDTreeRef:
     """ANN-style kd-tree (kdtree_ref.c): ann_kdtree_create(rows, n, dd, 1, ANN_KD_STD) + eps = 0 search."""
 

@@ -250,6 +250,32 @@ def test_kmodes_farthest_first_and_representatives(tb, oracle):
         tb.kmodes_representatives(Xr, lab + 5, Xr[:3])
 
 
+def test_reindex_matches_oracle(tb, oracle):
+    import torch
+    rng = np.random.default_rng(12)
+    ntiles = 5000
+    # zipf-like use counts with many ties and many unused tiles
+    tm = np.minimum(rng.zipf(1.3, 200000) - 1, ntiles - 1).astype(np.int32)
+    tm[rng.integers(0, len(tm), 3000)] = rng.integers(0, ntiles, 3000)
+    new, cnt, imap, order = tb.reindex(tm, ntiles)
+    wn, wc, wi, wo = oracle.reindex(tm, ntiles)
+    assert np.array_equal(new, wn) and np.array_equal(cnt, wc) and np.array_equal(imap, wi) and np.array_equal(order, wo)
+    # properties at a larger size: counts are non-increasing along the new order, the remap preserves use counts
+    assert np.all(np.diff(cnt[order]) <= 0)
+    assert np.array_equal(np.bincount(new, minlength=len(order)), cnt[order])
+    # device-pointer variant rewrites in place
+    d = torch.from_numpy(tm).cuda()
+    dc, di, do, nact = tb.reindex(d, ntiles)
+    torch.cuda.synchronize()
+    assert nact == len(wo) and np.array_equal(d.cpu().numpy(), wn) and np.array_equal(di.cpu().numpy(), wi)
+    # empty tilemap, out-of-range index
+    e = tb.reindex(np.zeros(0, np.int32), 4)
+    assert len(e[0]) == 0 and e[1].tolist() == [0, 0, 0, 0] and len(e[3]) == 0
+    from tiler_b200._lib import TMError
+    with pytest.raises(TMError):
+        tb.reindex(np.array([0, 9], np.int32), 4)
+
+
 def test_device_pointer_entry_points(tb, oracle, small_case):
     import torch
     ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])

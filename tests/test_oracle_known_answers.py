@@ -295,3 +295,13 @@ def test_prepare_frame_tiling_known_cases(oracle):
     r3, t3, _, a3, _ = o.prepare_frame_tiling(tiles, pals, [0], [1], quality=0, tile_flags=[0, 1, 0])
     i = int(np.where((a3 == 0) & (t3 == 1))[0][0])
     assert np.array_equal(r3[i], o.psyv(palpix=tiles[1], pal=pals[0], hmirror=True).astype(np.float32))
+
+
+def test_reindex_known_case(oracle):
+    # tiles 0..5; uses: tile 4 x3, tile 1 x3, tile 2 x1, tile 5 x2; tiles 0 and 3 unused
+    tm = np.array([4, 1, 4, 5, 2, 1, 4, 1, 5], np.int32)
+    new, cnt, imap, order = oracle.reindex(tm, 6)
+    assert cnt.tolist() == [0, 3, 1, 0, 3, 2]
+    assert order.tolist() == [1, 4, 5, 2]          # count desc, then old index asc (main.pas:4472-4481)
+    assert imap.tolist() == [-1, 0, 3, -1, 1, 2]
+    assert new.tolist() == [1, 0, 1, 2, 3, 0, 1, 0, 2]

@@ -253,3 +253,23 @@ def kmodes_representatives(X, labels, centroids, semantics=KM_ASM):
     cnt = np.empty(k, np.int32)
     check(lib.tm_kmodes_representatives(_hp(X), X.shape[0], _hp(labels), _hp(centroids), k, semantics, _hp(rep), _hp(cnt)))
     return rep, cnt
+
+
+def reindex(tilemap, ntiles):
+    """btnReindexClick + ReindexTiles (main.pas:1199-1230, 4483-4527).  numpy in: returns
+    (new_tilemap, use_count, idx_map, order[:n_active]); torch CUDA int32 tensor in: rewritten in place,
+    returns (use_count, idx_map, order, n_active) as tensors allocated like the input."""
+    act = C.c_int64()
+    if _is_dev(tilemap):
+        import torch
+        cnt = torch.empty(ntiles, dtype=torch.int32, device=tilemap.device)
+        imap = torch.empty_like(cnt)
+        order = torch.empty_like(cnt)
+        check(lib.tm_reindex_dev(_dp(tilemap), tilemap.numel(), int(ntiles), _dp(cnt), _dp(imap), _dp(order), C.byref(act)))
+        return cnt, imap, order, int(act.value)
+    tm = np.ascontiguousarray(tilemap, np.int32).copy()
+    cnt = np.empty(ntiles, np.int32)
+    imap = np.empty(ntiles, np.int32)
+    order = np.empty(ntiles, np.int32)
+    check(lib.tm_reindex(_hp(tm), tm.size, int(ntiles), _hp(cnt), _hp(imap), _hp(order), C.byref(act)))
+    return tm, cnt, imap, order[: act.value]

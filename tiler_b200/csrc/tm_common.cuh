@@ -108,3 +108,7 @@ int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32
                                      cudaStream_t s);
 int tm_launch_kmodes_umd(const uint8_t *d_X, int64_t np, const uint8_t *d_center, int sem,
                          uint64_t *d_mind, cudaStream_t s);
+
+// ---- reindex (reindex.cu): btnReindexClick main.pas:1199-1230 + ReindexTiles 4483-4527
+int tm_reindex_dev_impl(int32_t *d_tilemap, int64_t n, int64_t ntiles, int32_t *d_count, int32_t *d_idx_map,
+                        int32_t *d_order, int64_t *h_active, cudaStream_t s);
