@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU-baseline sample time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--kernels", action="store_true",
+                    help="also time the HBM-bound helper kernels and the KModes assignment pass (C4) and add them as `kernels`")
     ap.add_argument("--frames", type=int, default=0, help="override the clip length (profiling runs only)")
     return ap.parse_args()
 
@@ -225,6 +227,56 @@ def run_reference(args, rank, world):
         "gpu_launches": 0}))
 
 
+# ------------------------------------------------------------------ secondary kernels (reported under `kernels`)
+def helper_kernels(torch, tb, dev, stream, hbm_gbs, reps=3):
+    """Query-descriptor kernel (1 024 B / query), tileset pack (784 B / row) and the KModes assignment
+    pass on BASELINE config 4 (1 048 576 points x 16 384 centroids), CUDA events, best of `reps`."""
+    gen = torch.Generator(device=dev).manual_seed(0x42381337 + 99)
+
+    def timed(fn):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 1e30
+        for _ in range(reps):
+            e0.record(stream)
+            fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return best
+
+    out = {}
+    tiles, pal = synth_tileset(torch, 65536, 16, gen)
+    nq = 1 << 21
+    rgb = synth_queries(torch, nq, tiles[:4096], pal, gen)
+    desc = torch.empty((nq, 192), dtype=torch.float32, device=dev)
+    ms = timed(lambda: tb.psyv_queries(rgb, out=desc))
+    out["psyv_queries"] = {"queries": nq, "ms": ms, "algorithmic_bytes": nq * 1024, "achieved_gbs": nq * 1024 / ms / 1e6,
+                           "hbm_frac": nq * 1024 / ms / 1e6 / hbm_gbs}
+    del rgb, desc
+
+    def create():
+        tb.KDTree.from_tileset(tiles, pal.view(1, -1)).destroy()
+    ms = timed(create)
+    out["tileset_dataset_create"] = {"rows": 262144, "ms": ms,
+                                     "note": "pack/mirror kernel + mean/fp16 operand/norm-tile preparation, C3 tileset"}
+    npnt, k = 1 << 20, 1 << 14
+    t2, _ = synth_tileset(torch, npnt, 16, gen)
+    flags = torch.stack([(t2 == z).sum(1) > 1 for z in range(16)], 1).to(torch.uint8)  # zone flags, main.pas:4142-4165 (S = 16)
+    X = torch.cat([t2, flags], 1).contiguous()
+    cent = X[:: npnt // k][:k].contiguous()
+    clust = torch.empty(npnt, dtype=torch.int32, device=dev)
+    dis = torch.empty(npnt, dtype=torch.int64, device=dev)
+    ms = timed(lambda: tb.kmodes_assign(X, cent, tb.KM_ASM, out_clust=clust, out_dis=dis))
+    b = npnt * 92 + k * 80
+    out["kmodes_assign_c4"] = {"points": npnt, "centroids": k, "ms": ms, "pairs_per_s": npnt * k / ms * 1e3,
+                               "byte_compares_per_s": npnt * k * 80 / ms * 1e3, "algorithmic_bytes": b,
+                               "achieved_gbs": b / ms / 1e6,
+                               "bound": "integer ALU (HBM floor %.0f us)" % (b / hbm_gbs / 1e3)}
+    return out
+
+
 # ------------------------------------------------------------------ B200 arm
 def run_b200(args, rank, world, local_rank):
     import torch
@@ -335,6 +387,13 @@ def run_b200(args, rank, world, local_rank):
         launches = st["coarse_launches"] if st["coarse_launches"] else max(1, args.steps * ((nq + (1 << 21) - 1) >> 21))
         flops_total = 2.0 * nq * n_rows * D * args.steps
         achieved = flops_total / (search_ms / 1e3) / 1e12 if search_ms > 0 else None
+        # DRAM traffic of one full-size (2 097 152-query) launch of the search kernel, from the committed
+        # `ncu --set full` capture (dram__bytes_read.sum + dram__bytes_write.sum); see profiles/README.md
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "tc_search_traffic.json")))["dram_bytes_per_launch"]
+        except Exception:
+            pass
         peak = peaks.get("bf16_tflops_sustained") or 1400.0
         peak_src = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback"
         line = {
@@ -347,7 +406,7 @@ def run_b200(args, rank, world, local_rank):
                        "l2_policy": "inputs larger than L2 (query RGB %.2f GB per step)" % (nq * 256 / 1e9),
                        "engine": args.engine, "dataset_build_ms": dataset_build_ms},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
+                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
                          "kernel": "search (coarse tensor-core pass)" if st["coarse_launches"] else "search (exact SIMT)",
                          "kernel_ms_per_launch": search_ms / launches, "launches": launches,
                          "algorithmic_flops_per_launch": flops_total / launches},
@@ -359,6 +418,11 @@ def run_b200(args, rank, world, local_rank):
         }
         if e2e:
             line["e2e"] = e2e
+        if args.kernels and world == 1:
+            try:
+                line["kernels"] = helper_kernels(torch, tb, dev, stream, peaks.get("hbm_gbs") or 6500.0)
+            except Exception as e:  # secondary numbers must never cost the headline line
+                line["kernels"] = {"error": str(e)[:200]}
         if not args.no_cpu_baseline and world == 1:
             m = 1 << 15
             line["cpu_baseline"] = cpu_baseline(tiles.cpu().numpy(), pal.view(-1).cpu().numpy(), d_rgb[:m].cpu().numpy(),
