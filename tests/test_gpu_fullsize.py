@@ -1,0 +1,104 @@
+"""Parity at BASELINE.json's full sizes through size-independent properties (the oracle cannot finish
+these shapes in seconds): planted-query recovery, tensor-core engine == exact engine on a subsample,
+oracle check on a small subsample against the FULL dataset, KModes optimality of the returned labels."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env():
+    import torch
+    import tiler_b200 as tb
+    from bench import synth_queries, synth_tileset
+    tb.set_device(0)
+    dev = torch.device("cuda", 0)
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    return dict(torch=torch, tb=tb, dev=dev, gen=gen, synth_tileset=synth_tileset, synth_queries=synth_queries)
+
+
+def _render(torch, tiles, pal_i32, tid, hm, vm):
+    """exact render of tile tid in orientation (hm, vm) through the palette -> $00BBGGRR pixels"""
+    px = tiles[tid].view(-1, 8, 8).long()
+    px = torch.where(hm.view(-1, 1, 1), px.flip(2), px)
+    px = torch.where(vm.view(-1, 1, 1), px.flip(1), px)
+    return pal_i32[px.reshape(-1, 64)].contiguous()
+
+
+@pytest.mark.parametrize("ntiles,nq", [(16384, 1 << 20), (65536, 1 << 19)])  # C2 / C3 tilesets (N = 65 536 / 262 144 rows)
+def test_planted_queries_recovered_at_full_n(env, oracle, ntiles, nq):
+    torch, tb, dev, gen = env["torch"], env["tb"], env["dev"], env["gen"]
+    tiles, pal = env["synth_tileset"](torch, ntiles, 16, gen)
+    tid = torch.randint(0, ntiles, (nq,), generator=gen, device=dev)
+    hm = torch.randint(0, 2, (nq,), generator=gen, device=dev).bool()
+    vm = torch.randint(0, 2, (nq,), generator=gen, device=dev).bool()
+    rgb = _render(torch, tiles, pal, tid, hm, vm)
+    with tb.KDTree.from_tileset(tiles, pal.view(1, -1)) as t:
+        idx = torch.empty(nq, dtype=torch.int32, device=dev)
+        err = torch.empty(nq, dtype=torch.float32, device=dev)
+        tb.reset_stats()
+        t.frametiling_search(rgb, out_idx=idx, out_err=err)
+        torch.cuda.synchronize()
+        st = tb.stats()
+        # the query IS a dataset row: squared distance exactly 0, and the returned row renders to the same pixels
+        # (duplicate / symmetric tiles may legitimately return another row with identical pixels)
+        assert float(err.abs().max()) == 0.0
+        want = (tid.long() * 2 + vm.long()) * 2 + hm.long()  # row = ((p*T + t)*2 + vmir)*2 + hmir, main.pas:3902-3910
+        diff = (idx.long() != want).nonzero().flatten()
+        if len(diff):
+            got = idx[diff].long()
+            r2 = _render(torch, tiles, pal, got >> 2, (got & 1).bool(), ((got >> 1) & 1).bool())
+            assert torch.equal(r2, rgb[diff])
+            assert torch.all(got < want[diff])  # lowest row index among exact duplicates
+        assert st["fallback_queries"] <= nq // 100
+        # noisy queries: tensor-core engine == exact SIMT engine on a subsample, oracle on a smaller one
+        m = 8192
+        noisy = env["synth_queries"](torch, m, tiles, pal, gen)
+        i_tc = torch.empty(m, dtype=torch.int32, device=dev)
+        e_tc = torch.empty(m, dtype=torch.float32, device=dev)
+        t.frametiling_search(noisy, out_idx=i_tc, out_err=e_tc)
+        tb.set_engine(tb.ENGINE_SIMT)
+        try:
+            i_ex = torch.empty_like(i_tc)
+            e_ex = torch.empty_like(e_tc)
+            t.frametiling_search(noisy, out_idx=i_ex, out_err=e_ex)
+        finally:
+            tb.set_engine(tb.ENGINE_AUTO)
+        torch.cuda.synchronize()
+        assert torch.equal(i_tc, i_ex) and torch.equal(e_tc.view(torch.int32), e_ex.view(torch.int32))
+        o = oracle
+        sub = noisy[:256].cpu().numpy()
+        ds = o.psyv_tileset_f32(tiles.cpu().numpy(), pal.cpu().numpy())
+        oi, od, nxt = o.knn_f64(ds, o.psyv_queries_f32(sub), 1)
+        solid = (nxt - od[:, 0]) > 1e-5 * np.maximum(od[:, 0], 1e-12)
+        assert np.array_equal(i_tc[:256].cpu().numpy()[solid], oi[solid, 0])
+        assert np.allclose(e_tc[:256].cpu().numpy(), od[:, 0], rtol=1e-5, atol=1e-7)
+
+
+def test_kmodes_c4_properties(env, oracle):
+    """1 048 576 points x 16 384 centroids: planted points get dissimilarity 0, every returned (label, dis) pair is
+    consistent with a recomputation, and no sampled centroid beats the returned one."""
+    torch, tb, dev, gen = env["torch"], env["tb"], env["dev"], env["gen"]
+    npnt, k = 1 << 20, 1 << 14
+    t2, _ = env["synth_tileset"](torch, npnt, 16, gen)
+    flags = torch.stack([(t2 == z).sum(1) > 1 for z in range(16)], 1).to(torch.uint8)
+    X = torch.cat([t2, flags], 1).contiguous()
+    cent = X[:: npnt // k][:k].contiguous()
+    clust = torch.empty(npnt, dtype=torch.int32, device=dev)
+    dis = torch.empty(npnt, dtype=torch.int64, device=dev)
+    tb.kmodes_assign(X, cent, tb.KM_ASM, out_clust=clust, out_dis=dis)
+    torch.cuda.synchronize()
+    planted = torch.arange(0, npnt, npnt // k, device=dev)[:k]
+    assert torch.all(dis[planted] == 0)
+    # a planted point's label is the LAST centroid equal to it (kmodes.pas:414-415)
+    cl = clust[planted].long()
+    assert torch.equal(cent[cl], X[planted]) and torch.all(cl >= torch.arange(k, device=dev))
+    o = oracle
+    sel = torch.randint(0, npnt, (4096,), generator=gen, device=dev)
+    Xs, cs, ds_ = X[sel].cpu().numpy(), clust[sel].cpu().numpy(), dis[sel].cpu().numpy()
+    cn = cent.cpu().numpy()
+    for j in range(0, 4096, 64):  # recomputed dissimilarity of the returned pair
+        assert o.dissim(cn[cs[j]], Xs[j], o.ASM) == ds_[j]
+    wc, wd = o.kmodes_assign(Xs[:512], cn, o.ASM)  # full arg-min on a subsample against ALL centroids
+    assert np.array_equal(wc, cs[:512]) and np.array_equal(wd.astype(np.int64), ds_[:512])
