@@ -187,6 +187,16 @@ TM_API int tm_reindex(int32_t *h_tilemap, int64_t nitems, int64_t ntiles, int32_
 TM_API int tm_reindex_dev(int32_t *d_tilemap, int64_t nitems, int64_t ntiles, int32_t *d_use_count,
                           int32_t *d_idx_map, int32_t *d_order, int64_t *h_active);
 
+/* KModes rows on the device (WriteTileDatasetLine main.pas:4167-4183 + GetTilePalZoneThres 4142-4165):
+ * h_rows[ntiles][80] = 64 palette indices + 16 zone flags; h_signi[ntiles] (may be NULL) = PalSigni. */
+TM_API int tm_kmodes_rows(const uint8_t *h_palpix, int64_t ntiles, int pal_size, uint8_t *h_rows, int32_t *h_signi);
+/* DoFindBest of ReloadPreviousTiling (main.pas:4377-4409): like tm_kmodes_assign, but point i only sees the
+ * centroids (saved tiles) j with h_cbin[j] == h_xbin[i] (bins = PalSigni, 0 <= bin < nbins), in their
+ * original order; a point whose bin holds no centroid sees all of them.  clust = index into h_C. */
+TM_API int tm_kmodes_assign_binned(const uint8_t *h_X, int64_t npoints, const int32_t *h_xbin, const uint8_t *h_C,
+                                   int64_t k, const int32_t *h_cbin, int nbins, int semantics, int32_t *h_clust,
+                                   uint64_t *h_dis);
+
 /* counters since the last reset: kernel launches issued by this library, queries
  * that took the exact-fallback path after the tensor-core pass, and the device
  * time (ms, CUDA events) of the last search call split by phase. */

@@ -276,6 +276,33 @@ def test_reindex_matches_oracle(tb, oracle):
         tb.reindex(np.array([0, 9], np.int32), 4)
 
 
+def test_kmodes_rows_and_binned_assign(tb, oracle):
+    """K1 rows on the device and ReloadPreviousTiling's binned arg-min (main.pas:4377-4409)."""
+    o = oracle
+    for ps in (16, 8, 64):
+        tiles, _ = o.gen_tileset(o.BASE_SEED + 40 + ps, 1500, ps)
+        rows, signi = tb.kmodes_rows(tiles, ps)
+        for t in range(0, 1500, 7):
+            wr, ws = o.kmodes_row(tiles[t], ps)
+            assert np.array_equal(rows[t], wr) and signi[t] == ws, (ps, t)
+    tiles, _ = o.gen_tileset(o.BASE_SEED + 41, 4000)
+    saved, _ = o.gen_tileset(o.BASE_SEED + 42, 900)
+    X, xs = tb.kmodes_rows(tiles)
+    Cn, cs = tb.kmodes_rows(saved)
+    Cn[5] = Cn[300]; cs[5] = cs[300]  # duplicate saved tiles in one bin: the later one wins
+    clust, dis = tb.kmodes_assign_binned(X, xs, Cn, cs, 65)
+    # restated with the oracle's arg-min bin by bin
+    for i in range(0, 4000, 13):
+        members = np.where(cs == xs[i])[0]
+        if len(members):
+            j, d = o.min_dissim(Cn[members], X[i])
+            j = members[j]
+        else:
+            j, d = o.min_dissim(Cn, X[i])
+        assert clust[i] == j and dis[i] == d, i
+    assert np.any(~np.isin(xs, cs))  # some points fall into bins without saved tiles (the all-tiles branch ran)
+
+
 def test_device_pointer_entry_points(tb, oracle, small_case):
     import torch
     ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])

@@ -63,6 +63,8 @@ PROTOTYPES = {
     "tm_kmodes_representatives": (i32, [vp, i64, vp, vp, i64, i32, vp, vp]),
     "tm_reindex": (i32, [vp, i64, i64, vp, vp, vp, vp]),
     "tm_reindex_dev": (i32, [vp, i64, i64, vp, vp, vp, vp]),
+    "tm_kmodes_rows": (i32, [vp, i64, i32, vp, vp]),
+    "tm_kmodes_assign_binned": (i32, [vp, i64, vp, vp, i64, vp, i32, i32, vp, vp]),
     "tm_get_stats": (i32, [C.POINTER(TMStats)]),
     "tm_reset_stats": (i32, []),
     "tm_set_profiling": (i32, [i32]),

@@ -273,3 +273,25 @@ def reindex(tilemap, ntiles):
     order = np.empty(ntiles, np.int32)
     check(lib.tm_reindex(_hp(tm), tm.size, int(ntiles), _hp(cnt), _hp(imap), _hp(order), C.byref(act)))
     return tm, cnt, imap, order[: act.value]
+
+
+def kmodes_rows(palpix, pal_size=16):
+    """WriteTileDatasetLine + GetTilePalZoneThres (main.pas:4142-4183): returns (rows[n][80], signi[n])."""
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    rows = np.empty((palpix.shape[0], 80), np.uint8)
+    signi = np.empty(palpix.shape[0], np.int32)
+    check(lib.tm_kmodes_rows(_hp(palpix), palpix.shape[0], int(pal_size), _hp(rows), _hp(signi)))
+    return rows, signi
+
+
+def kmodes_assign_binned(X, xbin, centroids, cbin, nbins=65, semantics=KM_ASM):
+    """DoFindBest of ReloadPreviousTiling (main.pas:4377-4409)."""
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    centroids = np.ascontiguousarray(centroids, np.uint8).reshape(-1, 80)
+    xbin = np.ascontiguousarray(xbin, np.int32)
+    cbin = np.ascontiguousarray(cbin, np.int32)
+    clust = np.empty(X.shape[0], np.int32)
+    dis = np.empty(X.shape[0], np.uint64)
+    check(lib.tm_kmodes_assign_binned(_hp(X), X.shape[0], _hp(xbin), _hp(centroids), centroids.shape[0], _hp(cbin),
+                                      int(nbins), semantics, _hp(clust), _hp(dis)))
+    return clust, dis

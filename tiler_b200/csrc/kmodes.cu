@@ -314,6 +314,44 @@ __global__ void kmodes_rep_finish_kernel(const unsigned long long *__restrict__ 
     rep[j] = b == ~0ull ? -1 : (int32_t)(0xffffffffu - (uint32_t)(b & 0xffffffffull));
 }
 
+// ---- KModes rows (WriteTileDatasetLine main.pas:4167-4183 + GetTilePalZoneThres 4142-4165) ---------
+// row = 64 palette indices + 16 zone flags (flag z = 1 iff more than pal_size div 16 pixels fall into
+// zone b*16 div pal_size == z); signi = min over zones of (64 - count) (PalSigni, the bin key of
+// ReloadPreviousTiling main.pas:4393-4404).  One thread per tile, 16-byte loads / stores.
+__global__ void kmodes_rows_kernel(const uint8_t *__restrict__ palpix, int64_t ntiles, int pal_size,
+                                   uint8_t *__restrict__ rows, int32_t *__restrict__ signi) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntiles) return;
+    const uint4 *src = reinterpret_cast<const uint4 *>(palpix + t * 64);
+    uint4 *dst = reinterpret_cast<uint4 *>(rows + t * TM_KM_FEATURES);
+    uint32_t acc[16];
+#pragma unroll
+    for (int z = 0; z < 16; z++) acc[z] = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const uint4 v = __ldg(src + i);
+        dst[i] = v;
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int zone = (int)((w[j] >> (8 * b)) & 0xff) * 16 / pal_size;
+#pragma unroll
+                for (int z = 0; z < 16; z++) acc[z] += (zone == z); // registers only: no dynamic indexing
+            }
+    }
+    int res = 64;
+    uint32_t f[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int z = 0; z < 16; z++) {
+        res = min(res, 64 - (int)acc[z]);
+        f[z >> 2] |= (uint32_t)(acc[z] > (uint32_t)(pal_size / 16)) << (8 * (z & 3));
+    }
+    dst[4] = make_uint4(f[0], f[1], f[2], f[3]);
+    if (signi) signi[t] = res;
+}
+
 } // namespace
 
 namespace {
@@ -410,4 +448,13 @@ int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32
     kmodes_rep_finish_kernel<<<(unsigned)((k + 255) / 256), 256, 0, s>>>(d_best, k, d_rep);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "kmodes_rep_kernel");
+}
+
+int tm_launch_kmodes_rows(const uint8_t *d_palpix, int64_t ntiles, int pal_size, uint8_t *d_rows, int32_t *d_signi,
+                          cudaStream_t s) {
+    if (pal_size < 1 || pal_size > 256) { tm_set_error("pal_size must be in 1..256"); return TM_EINVAL; }
+    if (ntiles == 0) return 0;
+    kmodes_rows_kernel<<<(unsigned)((ntiles + 127) / 128), 128, 0, s>>>(d_palpix, ntiles, pal_size, d_rows, d_signi);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "kmodes_rows_kernel");
 }

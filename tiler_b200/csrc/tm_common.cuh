@@ -106,6 +106,8 @@ int tm_launch_kmodes_farthest_first(const uint8_t *d_X, int64_t np, int64_t k, i
 int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32_t *d_labels, const uint8_t *d_c, int64_t k,
                                      int sem, unsigned long long *d_best, int32_t *d_rep, int32_t *d_count, int *d_err,
                                      cudaStream_t s);
+int tm_launch_kmodes_rows(const uint8_t *d_palpix, int64_t ntiles, int pal_size, uint8_t *d_rows, int32_t *d_signi,
+                          cudaStream_t s);
 int tm_launch_kmodes_umd(const uint8_t *d_X, int64_t np, const uint8_t *d_center, int sem,
                          uint64_t *d_mind, cudaStream_t s);
 
