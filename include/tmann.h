@@ -197,6 +197,17 @@ TM_API int tm_kmodes_assign_binned(const uint8_t *h_X, int64_t npoints, const in
                                    int64_t k, const int32_t *h_cbin, int nbins, int semantics, int32_t *h_clust,
                                    uint64_t *h_dis);
 
+/* Temporal smoothing of a whole clip: btnSmoothClick (main.pas:1336-1370) + DoTemporalSmoothing (main.pas:4071-4119).
+ * h_palpix[ntiles][64] = FTiles[].PalPixels; h_pals[nkf][npal][pal_size] = PaletteRGB of every keyframe;
+ * h_frame_kf[nframes] = keyframe of every frame; h_tile / h_pal / h_attrs [nframes][npos] = TileMap (GlobalTileIndex,
+ * PalIdx, attrs bit0 HMirror, bit1 VMirror, bit2 Smoothed); strength = seTempoSmoo / 1000.  Outputs (each may be
+ * NULL) [nframes][npos]: SmoothedTileMap fields, and h_src_frame = the frame whose original TileMap item the
+ * smoothed item is a copy of (the Pascal side can copy the whole record, TmpIndex included, from there). */
+TM_API int tm_temporal_smoothing(const uint8_t *h_palpix, int64_t ntiles, const int32_t *h_pals, int nkf, int npal,
+                                 int pal_size, const int32_t *h_frame_kf, int64_t nframes, int64_t npos,
+                                 const int32_t *h_tile, const int32_t *h_pal, const uint8_t *h_attrs, double strength,
+                                 int32_t *h_src_frame, int32_t *h_out_tile, int32_t *h_out_pal, uint8_t *h_out_attrs);
+
 /* counters since the last reset: kernel launches issued by this library, queries
  * that took the exact-fallback path after the tensor-core pass, and the device
  * time (ms, CUDA events) of the last search call split by phase. */

@@ -111,6 +111,14 @@ void tmo_kmodes_representatives(const uint8_t *X, int64_t npoints, const int32_t
 /* WriteTileDatasetLine main.pas:4167-4183 + GetTilePalZoneThres 4142-4165 */
 int  tmo_kmodes_row(const uint8_t *palpix, int pal_size, uint8_t *row80);
 
+/* ---- smooth_ref.c ---------------------------------------------------- */
+/* btnSmoothClick main.pas:1336-1370 + DoTemporalSmoothing main.pas:4071-4119; attrs bit0 H, bit1 V, bit2 Smoothed;
+ * src_frame = frame whose original TileMap item the smoothed item is a copy of.  Returns -1 on bad indices. */
+int tmo_temporal_smoothing(const uint8_t *palpix, int64_t ntiles, const int32_t *pals, int nkf, int npal,
+                           int pal_size, const int32_t *frame_kf, int64_t nframes, int64_t npos,
+                           const int32_t *tile, const int32_t *pal, const uint8_t *attrs, double strength,
+                           int32_t *src_frame, int32_t *out_tile, int32_t *out_pal, uint8_t *out_attrs);
+
 /* ---- gen.c ----------------------------------------------------------- */
 /* RandInt kmodes.pas:82-86 */
 uint32_t tmo_randint(uint32_t range, uint32_t *seed);

@@ -306,6 +306,28 @@ def kmodes_rows(palpix, pal_size=16):
     return np.stack([kmodes_row(t, pal_size)[0] for t in palpix])
 
 
+def temporal_smoothing(palpix, pals, frame_kf, tile, pal, attrs, strength):
+    """btnSmoothClick + DoTemporalSmoothing (main.pas:1336-1370, 4071-4119).
+    pals [nkf][npal][pal_size]; tile/pal/attrs [nframes][npos].  Returns (src_frame, tile, pal, attrs)."""
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    pals = np.ascontiguousarray(pals, np.int32)
+    assert pals.ndim == 3
+    frame_kf = np.ascontiguousarray(frame_kf, np.int32)
+    tile = np.ascontiguousarray(tile, np.int32)
+    pal = np.ascontiguousarray(pal, np.int32)
+    attrs = np.ascontiguousarray(attrs, np.uint8)
+    nframes, npos = tile.shape
+    src = np.empty((nframes, npos), np.int32)
+    ot, op, oa = np.empty_like(tile), np.empty_like(pal), np.empty_like(attrs)
+    r = _lib.tmo_temporal_smoothing(_p(palpix, C.c_uint8), i64(palpix.shape[0]), _p(pals, C.c_int32), pals.shape[0],
+                                    pals.shape[1], pals.shape[2], _p(frame_kf, C.c_int32), i64(nframes), i64(npos),
+                                    _p(tile, C.c_int32), _p(pal, C.c_int32), _p(attrs, C.c_uint8), C.c_double(strength),
+                                    _p(src, C.c_int32), _p(ot, C.c_int32), _p(op, C.c_int32), _p(oa, C.c_uint8))
+    if r:
+        raise ValueError("temporal_smoothing: index out of range")
+    return src, ot, op, oa
+
+
 # ---- synthetic generators ---------------------------------------------------
 BASE_SEED = 0x42381337  # kmodes.pas:930
 

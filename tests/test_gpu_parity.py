@@ -303,6 +303,51 @@ def test_kmodes_rows_and_binned_assign(tb, oracle):
     assert np.any(~np.isin(xs, cs))  # some points fall into bins without saved tiles (the all-tiles branch ran)
 
 
+def _smoothing_case(o, seed, nframes, npos, ntiles, nkf, npal, change=0.35):
+    """Tilemaps that mostly persist from frame to frame, with near-duplicate tiles so that the
+    threshold test has hits, misses and both replacement directions."""
+    rng = np.random.default_rng(seed)
+    tiles, _ = o.gen_tileset(o.BASE_SEED + seed, ntiles)
+    near = tiles[: ntiles // 2].copy()  # second half: one-pixel variants of the first half
+    for t in range(near.shape[0]):
+        near[t, rng.integers(64)] = rng.integers(16)
+    tiles = np.concatenate([tiles[: ntiles - near.shape[0]], near])
+    pals = np.stack([np.stack([o.gen_palette(o.BASE_SEED + seed + 7 * k + p)[0] for p in range(npal)]) for k in range(nkf)])
+    frame_kf = np.sort(rng.integers(0, nkf, nframes)).astype(np.int32)
+    tile = np.empty((nframes, npos), np.int32)
+    pal = np.empty((nframes, npos), np.int32)
+    attrs = np.empty((nframes, npos), np.uint8)
+    tile[0] = rng.integers(0, ntiles, npos); pal[0] = rng.integers(0, npal, npos); attrs[0] = rng.integers(0, 8, npos)
+    half = ntiles - near.shape[0]
+    for f in range(1, nframes):
+        ch = rng.random(npos) < change
+        flip = rng.random(npos) < 0.5  # change to the near-duplicate (small distance) or to a random tile
+        twin = np.where(tile[f - 1] < near.shape[0], tile[f - 1] + half, tile[f - 1] - half) % ntiles
+        tile[f] = np.where(ch, np.where(flip, twin, rng.integers(0, ntiles, npos)), tile[f - 1])
+        pal[f] = np.where(ch & ~flip, rng.integers(0, npal, npos), pal[f - 1])
+        attrs[f] = np.where(ch & ~flip, rng.integers(0, 8, npos), attrs[f - 1]).astype(np.uint8)
+    return tiles, pals, frame_kf, tile, pal, attrs
+
+
+def test_temporal_smoothing_matches_oracle(tb, oracle):
+    """btnSmoothClick + DoTemporalSmoothing (main.pas:1336-1370, 4071-4119): bit-exact decisions."""
+    o = oracle
+    tiles, pals, frame_kf, tile, pal, attrs = _smoothing_case(o, 61, 24, 700, 400, 3, 4)
+    hits = []
+    for strength in (0.0, 0.01, 0.03, 0.1, 1.0):
+        want = o.temporal_smoothing(tiles, pals, frame_kf, tile, pal, attrs, strength)
+        got = tb.temporal_smoothing(tiles, pals, frame_kf, tile, pal, attrs, strength)
+        for w, g, name in zip(want, got, ("src_frame", "tile", "pal", "attrs")):
+            assert np.array_equal(w, g), (strength, name, int((w != g).sum()))
+        hits.append(int(((want[3] & 4) != 0).sum()))
+    assert hits[0] < hits[2] < hits[4]  # the thresholds separate the cases
+    # single frame / single keyframe boundary everywhere: nothing changes
+    src, t2, p2, a2 = tb.temporal_smoothing(tiles, pals, np.arange(3, dtype=np.int32), tile[:3], pal[:3], attrs[:3], 1.0)
+    assert np.array_equal(t2, tile[:3]) and np.array_equal(a2, attrs[:3]) and np.array_equal(src, np.repeat(np.arange(3), 700).reshape(3, 700))
+    with pytest.raises(Exception):
+        tb.temporal_smoothing(tiles, pals, frame_kf, tile + 400, pal, attrs, 0.1)
+
+
 def test_device_pointer_entry_points(tb, oracle, small_case):
     import torch
     ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])

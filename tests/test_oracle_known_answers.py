@@ -305,3 +305,41 @@ def test_reindex_known_case(oracle):
     assert order.tolist() == [1, 4, 5, 2]          # count desc, then old index asc (main.pas:4472-4481)
     assert imap.tolist() == [-1, 0, 3, -1, 1, 2]
     assert new.tolist() == [1, 0, 1, 2, 3, 0, 1, 0, 2]
+
+
+def test_temporal_smoothing_known_case(oracle):
+    """DoTemporalSmoothing (main.pas:4071-4119) on a hand-built chain of one position."""
+    o = oracle
+    flat = np.zeros((4, 64), np.uint8)
+    flat[1] = 1                     # tile 1: other flat colour
+    flat[2] = 0; flat[2, 0] = 1     # tile 2: tile 0 with one pixel changed
+    flat[3] = 0
+    pal = np.zeros((2, 1, 16), np.int32)
+    pal[:, 0, 0] = 0x000000
+    pal[:, 0, 1] = 0xFFFFFF
+    # flat white tile: luma DC term 64 * 1.0 * cQ/sqrt(16) * 0.5 = 32, chroma planes zero.  (gDCTLut's angle is
+    # (x + 0.5) * u * PI / 16, main.pas:621 - half the DCT-II frequency - so a flat tile has AC terms too.)
+    d = o.psyv(palpix=flat[1], pal=pal[0, 0], use_wavelets=False, qweighting=True)
+    assert abs(d[0] - 32.0) < 1e-12 and np.abs(d[64:]).max() < 1e-12
+    want1 = sum(np.cos((x + 0.5) * np.pi / 16.0) for x in range(8)) * 8 * (4.0 / np.sqrt(11.0)) * np.sqrt(0.5)
+    assert abs(d[1] - want1) < 1e-9
+    # frames: tile 2, tile 0, tile 0 | keyframe change | tile 1, tile 3 (different tile, same pixels as tile 0)
+    kf = np.array([0, 0, 0, 1, 1], np.int32)
+    tile = np.array([[2], [0], [0], [1], [3]], np.int32)
+    z = np.zeros((5, 1), np.int32)
+    at = np.zeros((5, 1), np.uint8)
+    d2 = o.psyv(palpix=flat[2], pal=pal[0, 0], use_wavelets=False, qweighting=True)
+    d0 = o.psyv(palpix=flat[0], pal=pal[0, 0], use_wavelets=False, qweighting=True)
+    cmp20 = np.sqrt(((d0 - d2) ** 2).sum() / 192.0)
+    # below the threshold of the 2 -> 0 pair: only identical items are merged
+    src, t, p, a = o.temporal_smoothing(flat, pal, kf, tile, z, at, cmp20 * 0.5)
+    assert t[:, 0].tolist() == [2, 0, 0, 1, 3] and a[:, 0].tolist() == [0, 0, 4, 0, 0]
+    assert src[:, 0].tolist() == [0, 1, 1, 3, 4]      # frame 2's item is a copy of frame 1's
+    # above it: frame 1 (tile 0 < tile 2) overwrites frame 0; frames 3, 4 differ by a full white tile
+    src, t, p, a = o.temporal_smoothing(flat, pal, kf, tile, z, at, cmp20 * 1.5)
+    assert t[:, 0].tolist() == [0, 0, 0, 1, 3] and a[:, 0].tolist() == [0, 4, 4, 0, 0]
+    assert src[:, 0].tolist() == [1, 1, 1, 3, 4]
+    # large threshold: inside keyframe 1 tile 3 >= tile 1, so frame 4 takes frame 3's item; no merge across keyframes
+    src, t, p, a = o.temporal_smoothing(flat, pal, kf, tile, z, at, 10.0)
+    assert t[:, 0].tolist() == [0, 0, 0, 1, 1] and a[:, 0].tolist() == [0, 4, 4, 0, 4]
+    assert src[:, 0].tolist() == [1, 1, 1, 3, 3]

@@ -65,6 +65,7 @@ PROTOTYPES = {
     "tm_reindex_dev": (i32, [vp, i64, i64, vp, vp, vp, vp]),
     "tm_kmodes_rows": (i32, [vp, i64, i32, vp, vp]),
     "tm_kmodes_assign_binned": (i32, [vp, i64, vp, vp, i64, vp, i32, i32, vp, vp]),
+    "tm_temporal_smoothing": (i32, [vp, i64, vp, i32, i32, i32, vp, i64, i64, vp, vp, vp, C.c_double, vp, vp, vp, vp]),
     "tm_get_stats": (i32, [C.POINTER(TMStats)]),
     "tm_reset_stats": (i32, []),
     "tm_set_profiling": (i32, [i32]),

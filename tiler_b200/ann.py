@@ -295,3 +295,23 @@ def kmodes_assign_binned(X, xbin, centroids, cbin, nbins=65, semantics=KM_ASM):
     check(lib.tm_kmodes_assign_binned(_hp(X), X.shape[0], _hp(xbin), _hp(centroids), centroids.shape[0], _hp(cbin),
                                       int(nbins), semantics, _hp(clust), _hp(dis)))
     return clust, dis
+
+
+def temporal_smoothing(palpix, pals, frame_kf, tile, pal, attrs, strength):
+    """btnSmoothClick + DoTemporalSmoothing (main.pas:1336-1370, 4071-4119) for a whole clip.
+    pals [nkf][npal][pal_size]; tile / pal / attrs [nframes][npos].  Returns (src_frame, tile, pal, attrs)."""
+    palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
+    pals = np.ascontiguousarray(pals, np.int32)
+    if pals.ndim != 3:
+        raise ValueError("pals must be [nkf][npal][pal_size]")
+    frame_kf = np.ascontiguousarray(frame_kf, np.int32)
+    tile = np.ascontiguousarray(tile, np.int32)
+    pal = np.ascontiguousarray(pal, np.int32)
+    attrs = np.ascontiguousarray(attrs, np.uint8)
+    nframes, npos = tile.shape
+    src = np.empty((nframes, npos), np.int32)
+    ot, op, oa = np.empty_like(tile), np.empty_like(pal), np.empty_like(attrs)
+    check(lib.tm_temporal_smoothing(_hp(palpix), palpix.shape[0], _hp(pals), pals.shape[0], pals.shape[1], pals.shape[2],
+                                    _hp(frame_kf), nframes, npos, _hp(tile), _hp(pal), _hp(attrs), float(strength),
+                                    _hp(src), _hp(ot), _hp(op), _hp(oa)))
+    return src, ot, op, oa

@@ -245,6 +245,135 @@ __global__ void global_rows_kernel(const uint8_t *__restrict__ palpix, int64_t n
     reinterpret_cast<float4 *>(out)[i] = make_float4(v[0], v[1], v[2], v[3]);
 }
 
+// ---- temporal smoothing (btnSmoothClick main.pas:1336-1370, DoTemporalSmoothing main.pas:4071-4119) -------------
+// A tilemap position is a chain of items along the frame axis: step f compares the (possibly already replaced)
+// item of frame f-1 with the original item of frame f, so frames are sequential and positions independent.  One
+// warp owns one position and walks the frames; the descriptor of the carried item stays in shared memory, so
+// each step renders at most one new Q-weighted DCT descriptor (lanes = 6 coefficients each, 64 sequential
+// multiply-adds in the reference's order) and none when the two items are the same (tile, palette, mirrors):
+// identical descriptors give cmp = 0 exactly.  The 192-term squared-difference sum is sequential like
+// CompareEuclideanDCTPtr (main.pas:659-675).
+constexpr int TS_WARPS = 8;
+constexpr size_t TS_SMEM = sizeof(PsyvTables) + sizeof(double) * (4096 + 64 + 192 + TS_WARPS * 4 * 192);
+
+struct TsItem {
+    int tile, pal, attrs, src;
+};
+
+__device__ __forceinline__ void ts_descriptor(const TsItem &it, const uint8_t *__restrict__ palpix,
+                                              const int32_t *__restrict__ kpal, int pal_size, const PsyvTables &T,
+                                              const PsyvConsts &K, const double *lutT, const double *ratio,
+                                              const double *qw, double *cpn, double *d, int lane, int *bad) {
+    const int hm = it.attrs & 1, vm = (it.attrs >> 1) & 1;
+    const int32_t *pal = kpal + (int64_t)it.pal * pal_size;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        const int o = lane + 32 * k, x = o & 7, y = o >> 3;
+        const int xx = hm ? 7 - x : x, yy = vm ? 7 - y : y; // main.pas:3041-3046
+        int pi = palpix[(int64_t)it.tile * 64 + yy * 8 + xx];
+        if (pi >= pal_size) { *bad = 1; pi = 0; }
+        const int32_t col = __ldg(pal + pi);
+        cpn[o] = plane_value(col, 0, &T, K);
+        cpn[64 + o] = plane_value(col, 1, &T, K);
+        cpn[128 + o] = plane_value(col, 2, &T, K);
+    }
+    __syncwarp();
+    double z[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    const int vu0 = lane, vu1 = lane + 32;
+#pragma unroll 4
+    for (int i = 0; i < 64; i++) { // main.pas:3083-3166, sequential in (y, x)
+        const double l0 = lutT[i * 64 + vu0], l1 = lutT[i * 64 + vu1];
+        const double c0 = cpn[i], c1 = cpn[64 + i], c2 = cpn[128 + i];
+        z[0] += c0 * l0; z[1] += c0 * l1;
+        z[2] += c1 * l0; z[3] += c1 * l1;
+        z[4] += c2 * l0; z[5] += c2 * l1;
+    }
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        const int c = lane + 32 * j;
+        d[c] = (z[j] * qw[c]) * ratio[c & 63]; // z *= cDCTQuantization; pDCT^ := z * pRatio^ (main.pas:3168-3171)
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(TS_WARPS * 32) temporal_smoothing_kernel(
+    const uint8_t *__restrict__ palpix, int64_t ntiles, const int32_t *__restrict__ pals, int npal, int pal_size,
+    const int32_t *__restrict__ frame_kf, int64_t nframes, int64_t npos, const int32_t *__restrict__ tile,
+    const int32_t *__restrict__ pal, const uint8_t *__restrict__ attrs, double strength,
+    const PsyvTables *__restrict__ tabs, PsyvConsts K, const double *__restrict__ lut, const double *__restrict__ qwg,
+    int32_t *__restrict__ src_frame, int32_t *__restrict__ out_tile, int32_t *__restrict__ out_pal,
+    uint8_t *__restrict__ out_attrs, int *__restrict__ bad) {
+    extern __shared__ __align__(16) uint8_t tsm[];
+    PsyvTables &T = *reinterpret_cast<PsyvTables *>(tsm);
+    double *lutT = reinterpret_cast<double *>(tsm + sizeof(PsyvTables)); // [i][vu]: lanes read consecutive words
+    double *ratio = lutT + 4096;
+    double *qw = ratio + 64;
+    double *wbuf = qw + 192;
+    for (int i = threadIdx.x; i < (int)(sizeof(PsyvTables) / 8); i += blockDim.x)
+        reinterpret_cast<double *>(&T)[i] = reinterpret_cast<const double *>(tabs)[i];
+    for (int i = threadIdx.x; i < 4096; i += blockDim.x) lutT[(i & 63) * 64 + (i >> 6)] = lut[i];
+    for (int i = threadIdx.x; i < 64; i += blockDim.x) ratio[i] = lut[4096 + i];
+    for (int i = threadIdx.x; i < 192; i += blockDim.x) qw[i] = qwg[i];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *cpn = wbuf + warp * 4 * 192, *dP = cpn + 192, *dC = dP + 192, *sq = dC + 192;
+    const double sqrt_factor = 1.0 / (8.0 * 8.0 * 3.0); // cSqrtFactor main.pas:4073
+    int lbad = 0;
+    for (int64_t p = (int64_t)blockIdx.x * TS_WARPS + warp; p < npos; p += (int64_t)gridDim.x * TS_WARPS) {
+        TsItem prev{tile[p], pal[p], attrs[p], 0};
+        if (prev.tile < 0 || prev.tile >= ntiles || prev.pal < 0 || prev.pal >= npal) { lbad = 1; prev.tile = 0; prev.pal = 0; }
+        bool have_prev = false; // dP holds prev's descriptor
+        int kf_prev = frame_kf[0];
+        for (int64_t f = 1; f < nframes; f++) {
+            const int64_t c = f * npos + p;
+            TsItem cur{tile[c], pal[c], attrs[c], (int)f};
+            if (cur.tile < 0 || cur.tile >= ntiles || cur.pal < 0 || cur.pal >= npal) { lbad = 1; cur.tile = 0; cur.pal = 0; }
+            const int kf = frame_kf[f];
+            if (kf == kf_prev) { // main.pas:4082-4083: only inside one keyframe
+                double cmp = 0.0;
+                const bool same = cur.tile == prev.tile && cur.pal == prev.pal && ((cur.attrs ^ prev.attrs) & 3) == 0;
+                if (!same) {
+                    const int32_t *kpal = pals + (int64_t)kf * npal * pal_size;
+                    if (!have_prev) ts_descriptor(prev, palpix, kpal, pal_size, T, K, lutT, ratio, qw, cpn, dP, lane, &lbad);
+                    ts_descriptor(cur, palpix, kpal, pal_size, T, K, lutT, ratio, qw, cpn, dC, lane, &lbad);
+                    have_prev = true;
+#pragma unroll
+                    for (int j = 0; j < 6; j++) {
+                        const double e = dC[lane + 32 * j] - dP[lane + 32 * j];
+                        sq[lane + 32 * j] = e * e;
+                    }
+                    __syncwarp();
+                    for (int i = 0; i < 192; i++) cmp += sq[i]; // every lane: same sequential sum, no broadcast needed
+                    cmp = sqrt(cmp * sqrt_factor);
+                    __syncwarp();
+                }
+                bool cur_desc_is_dC = !same;
+                if (fabs(cmp) <= strength) {
+                    if (cur.tile >= prev.tile) { cur = prev; cur_desc_is_dC = false; } // TMI^ := PrevTMI^
+                    else prev = cur;                                                   // PrevTMI^ := TMI^
+                    cur.attrs |= 4;
+                } else {
+                    cur.attrs &= ~4;
+                }
+                if (cur_desc_is_dC) { double *t = dP; dP = dC; dC = t; }
+            } else {
+                have_prev = false;
+            }
+            if (lane == 0) {
+                const int64_t q = c - npos;
+                src_frame[q] = prev.src; out_tile[q] = prev.tile; out_pal[q] = prev.pal; out_attrs[q] = (uint8_t)prev.attrs;
+            }
+            prev = cur;
+            kf_prev = kf;
+        }
+        if (lane == 0 && nframes > 0) {
+            const int64_t q = (nframes - 1) * npos + p;
+            src_frame[q] = prev.src; out_tile[q] = prev.tile; out_pal[q] = prev.pal; out_attrs[q] = (uint8_t)prev.attrs;
+        }
+    }
+    if (lbad) atomicOr(bad, 1);
+}
+
 struct PsyvDeviceState {
     PsyvTables *tabs[3] = {nullptr, nullptr, nullptr}; // gamma -1, 0, 1
     double *lut = nullptr;                            // 4096 DCT lut + 64 cUVRatio
@@ -375,4 +504,27 @@ int tm_launch_global_rows(const uint8_t *d_palpix, int64_t ntiles, float *d_out,
     global_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_palpix, ntiles, d_out);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "global_rows_kernel");
+}
+
+int tm_launch_temporal_smoothing(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal, int pal_size,
+                                 const int32_t *d_frame_kf, int64_t nframes, int64_t npos, const int32_t *d_tile,
+                                 const int32_t *d_pal, const uint8_t *d_attrs, double strength, int32_t *d_src_frame,
+                                 int32_t *d_out_tile, int32_t *d_out_pal, uint8_t *d_out_attrs, int *d_bad,
+                                 cudaStream_t s) {
+    if (nframes == 0 || npos == 0) return 0;
+    int r = ensure_tables();
+    if (r) return r;
+    static bool attr = false;
+    if (!attr) {
+        TM_CUDA(cudaFuncSetAttribute(temporal_smoothing_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TS_SMEM));
+        attr = true;
+    }
+    const int64_t blocks = (npos + TS_WARPS - 1) / TS_WARPS;
+    const unsigned grid = (unsigned)(blocks < 148 * 8 ? blocks : 148 * 8);
+    temporal_smoothing_kernel<<<grid, TS_WARPS * 32, TS_SMEM, s>>>(d_palpix, ntiles, d_pals, npal, pal_size, d_frame_kf,
+                                                                  nframes, npos, d_tile, d_pal, d_attrs, strength,
+                                                                  g_ps.tabs[0], make_consts(), g_ps.lut, g_ps.qw,
+                                                                  d_src_frame, d_out_tile, d_out_pal, d_out_attrs, d_bad);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "temporal_smoothing_kernel");
 }

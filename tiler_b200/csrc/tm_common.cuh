@@ -106,6 +106,11 @@ int tm_launch_kmodes_farthest_first(const uint8_t *d_X, int64_t np, int64_t k, i
 int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32_t *d_labels, const uint8_t *d_c, int64_t k,
                                      int sem, unsigned long long *d_best, int32_t *d_rep, int32_t *d_count, int *d_err,
                                      cudaStream_t s);
+int tm_launch_temporal_smoothing(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal, int pal_size,
+                                 const int32_t *d_frame_kf, int64_t nframes, int64_t npos, const int32_t *d_tile,
+                                 const int32_t *d_pal, const uint8_t *d_attrs, double strength, int32_t *d_src_frame,
+                                 int32_t *d_out_tile, int32_t *d_out_pal, uint8_t *d_out_attrs, int *d_bad,
+                                 cudaStream_t s);
 int tm_launch_kmodes_rows(const uint8_t *d_palpix, int64_t ntiles, int pal_size, uint8_t *d_rows, int32_t *d_signi,
                           cudaStream_t s);
 int tm_launch_kmodes_umd(const uint8_t *d_X, int64_t np, const uint8_t *d_center, int sem,
