@@ -128,6 +128,54 @@ def test_legacy_entry_points(tb, oracle, small_case):
     t.destroy()  # idempotent / NULL-safe
 
 
+def test_concurrent_callers_share_handles(tb, oracle, small_case):
+    """The reference calls ANN from a pool of worker threads over one shared tree (DoFrameTiling, one frame per
+    thread, main.pas:972 -> 4033): concurrent calls of every flavour must return what serial calls return."""
+    import threading
+    ds = oracle.psyv_tileset_f32(small_case["tiles"][:256], small_case["pal"])
+    t = tb.KDTree.create(ds)
+    ft = tb.KDTree.from_tileset(small_case["tiles"], small_case["pal"])
+    rgb = small_case["rgb"]
+    q = oracle.psyv_queries_f32(rgb[:64])
+    X = oracle.kmodes_rows(small_case["tiles"][:600])
+    Cn = X[::7].copy()
+    want_single = [t.search(q[i]) for i in range(64)]
+    want_batch = t.search_batch(q, 4)
+    want_ft = [ft.frametiling_search(rgb[o:o + 300 + 17 * j]) for j, o in enumerate(range(0, 1200, 300))]
+    want_km = [tb.kmodes_assign(X[o:o + 150], Cn[: 20 + 11 * j]) for j, o in enumerate(range(0, 600, 150))]
+    errors = []
+
+    def worker(w):
+        try:
+            for rep in range(6):
+                kind = (w + rep) % 4
+                if kind == 0:
+                    for i in range(w, 64, 8):
+                        assert t.search(q[i]) == want_single[i]
+                elif kind == 1:
+                    gi, ge = t.search_batch(q, 4)
+                    assert np.array_equal(gi, want_batch[0]) and np.array_equal(ge, want_batch[1])
+                elif kind == 2:
+                    j = (w + rep) % 4
+                    gi, ge = ft.frametiling_search(rgb[300 * j:300 * j + 300 + 17 * j])
+                    assert np.array_equal(gi, want_ft[j][0]) and np.array_equal(ge, want_ft[j][1])
+                else:
+                    j = (w + rep) % 4
+                    gc, gd = tb.kmodes_assign(X[150 * j:150 * j + 150], Cn[: 20 + 11 * j])
+                    assert np.array_equal(gc, want_km[j][0]) and np.array_equal(gd, want_km[j][1])
+        except BaseException as e:  # noqa: BLE001 - reported in the main thread
+            errors.append((w, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(w,)) for w in range(8)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors[:3]
+    t.destroy()
+    ft.destroy()
+
+
 def test_search_edge_cases(tb, oracle):
     rng = np.random.default_rng(0)
     # ragged sizes: n not a multiple of the tile, nq not a multiple of the block, dd not a multiple of 4

@@ -12,6 +12,11 @@ std::atomic<int64_t> g_launches{0}, g_queries{0}, g_fallbacks{0};
 int g_engine = TM_ENGINE_AUTO;
 
 namespace {
+// The reference calls the library from a pool of worker threads over shared handles (DoFrameTiling, one frame per
+// thread, main.pas:972).  All device work goes through one stream and grow-only scratch, so every entry point that
+// touches the device runs under one process-wide lock (recursive: entry points call each other).
+std::recursive_mutex g_api_mu;
+#define TM_API_GUARD std::lock_guard<std::recursive_mutex> api_guard_(g_api_mu)
 thread_local char t_err[512] = "";
 std::mutex g_init_mu;
 bool g_inited = false;
@@ -130,6 +135,7 @@ const char *tm_last_error(void) { return t_err; }
 int tm_version(void) { return 100; }
 
 int tm_set_device(int device) {
+    TM_API_GUARD;
     {
         std::lock_guard<std::mutex> lk(g_init_mu);
         if (g_inited && device != g_device) {
@@ -148,6 +154,7 @@ int tm_set_engine(int engine) {
 }
 
 int tm_set_stream(void *cuda_stream) {
+    TM_API_GUARD;
     int r = tm_ensure_device();
     if (r) return r;
     cudaStreamSynchronize(g_stream);
@@ -157,6 +164,7 @@ int tm_set_stream(void *cuda_stream) {
 }
 
 int tm_device_sync(void) {
+    TM_API_GUARD;
     int r = tm_ensure_device();
     if (r) return r;
     return tm_check(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
@@ -200,6 +208,7 @@ static ANNkdtree *finish_handle(ANNkdtree *h) {
 }
 
 ANNkdtree *tm_dataset_create(const float *rows, int64_t n, int dd, int is_device) {
+    TM_API_GUARD;
     if (tm_ensure_device()) return nullptr;
     if (n < 0 || dd < 1 || (n > 0 && !rows)) { tm_set_error("tm_dataset_create: bad arguments"); return nullptr; }
     if (n > 0x7fffffff) { tm_set_error("tm_dataset_create: n too large"); return nullptr; }
@@ -215,6 +224,7 @@ ANNkdtree *tm_dataset_create(const float *rows, int64_t n, int dd, int is_device
 }
 
 ANNkdtree *ann_kdtree_create(float **pa, int n, int dd, int bs, int split) {
+    TM_API_GUARD;
     (void)bs; (void)split;
     if (n < 0 || dd < 1 || (n > 0 && !pa)) { tm_set_error("ann_kdtree_create: bad arguments"); return nullptr; }
     // rows are separately allocated Pascal dynamic arrays (main.pas:3757, 3955): gather them
@@ -224,6 +234,7 @@ ANNkdtree *ann_kdtree_create(float **pa, int n, int dd, int bs, int split) {
 }
 
 void ann_kdtree_destroy(ANNkdtree *akd) {
+    TM_API_GUARD;
     if (!akd || akd->magic != TM_MAGIC) return; // NULL-safe like the reference wrapper
     cudaSetDevice(akd->device);
     cudaStreamSynchronize(g_stream);
@@ -234,6 +245,7 @@ int64_t tm_dataset_rows(const ANNkdtree *akd) { return valid(akd) ? -1 : akd->n;
 int tm_dataset_dim(const ANNkdtree *akd) { return valid(akd) ? -1 : akd->dd; }
 
 int tm_dataset_read(const ANNkdtree *akd, float *h_rows) {
+    TM_API_GUARD;
     int r = valid(akd);
     if (r) return r;
     if ((r = tm_ensure_device())) return r;
@@ -257,6 +269,7 @@ static int search_dev(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_
 }
 
 int tm_search_batch_dev(ANNkdtree *akd, const float *d_q, int64_t nq, int k, int *d_idxs, float *d_errs) {
+    TM_API_GUARD;
     int r = valid(akd);
     if (r) return r;
     if ((r = tm_ensure_device())) return r;
@@ -268,6 +281,7 @@ int tm_search_batch_dev(ANNkdtree *akd, const float *d_q, int64_t nq, int k, int
 }
 
 int ann_kdtree_search_batch(ANNkdtree *akd, const float *h_q, int64_t nq, int k, int *h_idxs, float *h_errs) {
+    TM_API_GUARD;
     int r = valid(akd);
     if (r) return r;
     if ((r = tm_ensure_device())) return r;
@@ -303,6 +317,7 @@ static int search_one(ANNkdtree *akd, const float *q, int k, int *idxs, float *e
 }
 
 int ann_kdtree_search(ANNkdtree *akd, float *q, float eps, float *err) {
+    TM_API_GUARD;
     (void)eps;
     int idx = -1;
     float e = 0.f; // the reference wrapper pre-sets idx = -1, dist = 0
@@ -314,6 +329,7 @@ int ann_kdtree_search(ANNkdtree *akd, float *q, float eps, float *err) {
 int ann_kdtree_pri_search(ANNkdtree *akd, float *q, float eps, float *err) { return ann_kdtree_search(akd, q, eps, err); }
 
 int ann_kdtree_search_multi(ANNkdtree *akd, int *idxs, float *errs, int cnt, float *q, float eps) {
+    TM_API_GUARD;
     (void)eps;
     if (cnt <= 0 || !idxs) return 0;
     if (cnt <= 16) { search_one(akd, q, cnt, idxs, errs); return 0; }
