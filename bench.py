@@ -391,7 +391,9 @@ def run_b200(args, rank, world, local_rank):
         # `ncu --set full` capture (dram__bytes_read.sum + dram__bytes_write.sum); see profiles/README.md
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "tc_search_traffic.json")))["dram_bytes_per_launch"]
+            tj = json.load(open(os.path.join(ROOT, "profiles", "tc_search_traffic.json")))
+            if tj["dataset_rows"] == n_rows and nq >= tj["queries_per_launch"]:  # the capture is of this workload's launch
+                traffic = tj["dram_bytes_per_launch"]
         except Exception:
             pass
         peak = peaks.get("bf16_tflops_sustained") or 1400.0

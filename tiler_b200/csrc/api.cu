@@ -254,15 +254,23 @@ int tm_dataset_read(const ANNkdtree *akd, float *h_rows) {
 }
 
 // engine dispatch; everything on g_stream, no host sync inside
-static int search_dev(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err) {
+// engine choice for one batch (TM_ENGINE_*), or -1 with the error set
+static int pick_engine(ANNkdtree *h, int64_t nq) {
+    const bool tc_ok = (h->rows_f16 != nullptr) && h->n >= 1;
+    int engine = g_engine;
+    if (engine == TM_ENGINE_TC && !tc_ok) { tm_set_error("tensor-core engine unavailable for this dataset (dd=%d)", h->dd); return -1; }
+    if (engine == TM_ENGINE_AUTO) engine = (tc_ok && nq >= 64) ? TM_ENGINE_TC : TM_ENGINE_SIMT;
+    return engine;
+}
+
+static int search_dev(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, bool operand_ready = false) {
     if (k < 1 || k > 16) { tm_set_error("k must be in 1..16 (got %d)", k); return TM_EINVAL; }
     g_queries.fetch_add(nq, std::memory_order_relaxed);
-    bool tc_ok = (h->rows_f16 != nullptr) && h->n >= 1;
-    int engine = g_engine;
-    if (engine == TM_ENGINE_TC && !tc_ok) { tm_set_error("tensor-core engine unavailable for this dataset (dd=%d)", h->dd); return TM_EINVAL; }
-    if (engine == TM_ENGINE_AUTO) engine = (tc_ok && nq >= 64) ? TM_ENGINE_TC : TM_ENGINE_SIMT;
+    const int engine = pick_engine(h, nq);
+    if (engine < 0) return TM_EINVAL;
     int tok = tm_prof_begin(1, g_stream);
-    int r = (engine == TM_ENGINE_TC) ? tm_search_tc(h, d_q, nq, k, d_idx, d_err, g_stream)
+    int r = (engine == TM_ENGINE_TC) ? (operand_ready ? tm_search_tc_prepared(h, d_q, nq, k, d_idx, d_err, g_stream)
+                                                      : tm_search_tc(h, d_q, nq, k, d_idx, d_err, g_stream))
                                      : tm_launch_search_simt(h->rows_f32, h->n, h->dd, d_q, nq, k, d_idx, d_err, g_stream);
     tm_prof_end(tok, g_stream);
     return r;

@@ -13,6 +13,7 @@
 // HBM-bound by design: 256 B in, 768 B out per query tile.
 #include "tm_common.cuh"
 #include <math.h>
+#include <cuda_fp16.h>
 
 namespace {
 
@@ -24,7 +25,7 @@ struct PsyvTables {      // host-built, mirrors InitLuts main.pas:592-623
 };
 
 struct PsyvConsts {
-    double cu, cv, luma_div, luma_rcp, haar;
+    double cu, cv, luma_div, luma_rcp, haar, rcp255;
 };
 
 __device__ double *g_dct_lut_dev = nullptr; // unused placeholder (lut passed by pointer)
@@ -95,14 +96,43 @@ __device__ __forceinline__ void dct_plane(const double (&a)[64], const double *l
     }
 }
 
-// Shared-memory staging of one block's 64 tiles: the block's input (64 x 256 B) and output
-// (64 x 768 B) are both contiguous in global memory, so they move with fully coalesced 16-byte
-// accesses, while each thread reads / writes its own (tile, plane) slice in shared memory.  Row
-// strides are padded to 4 (mod 32) words so the 16-byte per-thread accesses are bank-conflict free.
-constexpr int PQ_TILES = 64;
-constexpr int PQ_IN_STRIDE = 68;   // words per staged input tile (64 + 4)
+// Query tiles, two phases per block of 32 tiles (96 threads):
+//   1. pixel phase: consecutive threads take consecutive pixels straight from global memory (coalesced), compute
+//      (y, u, v) ONCE per pixel and park them as doubles in shared memory.  With GammaCor = -1 the colour LUT
+//      gGammaCorLut[c] = c / 255.0 (main.pas:596-601) is evaluated arithmetically (exact 3-operation division,
+//      checked against c / 255.0 for all 256 values when the tables are built), which removes the random-index
+//      shared-memory reads whose bank conflicts bounded the one-phase kernel (11 LUT reads per pixel, ~5-way).
+//   2. plane phase: thread = (tile, plane) pulls its 64 doubles into registers (16-byte reads, row stride 66
+//      doubles = 4 banks apart -> conflict free), runs the Haar / DCT, and stages the float row in the same
+//      shared memory (dead by then) for a coalesced 16-byte store.
+constexpr int PQ_TILES = 32;
+constexpr int PQ_THREADS = 96;
+constexpr int PQ_CPN_STRIDE = 66;  // doubles per (plane, tile) row
 constexpr int PQ_OUT_STRIDE = 196; // words per staged output row (192 + 4)
-constexpr size_t PQ_SMEM = sizeof(PsyvTables) + (size_t)PQ_TILES * (PQ_IN_STRIDE + PQ_OUT_STRIDE) * 4;
+constexpr size_t PQ_CPN_BYTES = (size_t)3 * PQ_TILES * PQ_CPN_STRIDE * 8;
+constexpr size_t PQ_SMEM_LINEAR = PQ_CPN_BYTES;
+constexpr size_t PQ_SMEM_LUT = PQ_CPN_BYTES + 256 * 8;
+static_assert((size_t)PQ_TILES * PQ_OUT_STRIDE * 4 <= PQ_CPN_BYTES, "output staging aliases the component buffer");
+
+// Optional second output of the query kernel: the tensor-core engine's centred fp16 operand and the two norms
+// the certificate needs (what search_tc.cu's operand_kernel derives from the float rows), written from the
+// staged rows so the 768 B / query are not read back from HBM.  q16 == nullptr: not requested.
+struct PsyvOperandOut {
+    const float *mean; // dataset column means [192]
+    __half *q16;       // [nq][192]
+    float *qn16;       // sum of squares of the rounded values
+    float *qne;        // Euclidean norm of the centred float row
+};
+
+template <bool LINEAR>
+__device__ __forceinline__ double channel_value(int c, const double *ftab, double rcp255) {
+    if (LINEAR) { // c / 255.0: q = RN(c * RN(1/255)), r = c - 255 q (exact), RN(q + r * RN(1/255))
+        const double cd = (double)c;
+        const double q0 = cd * rcp255;
+        return fma(fma(-q0, 255.0, cd), rcp255, q0);
+    }
+    return ftab[c];
+}
 
 __device__ __forceinline__ void store_row_smem(float *dst, const double (&a)[64]) {
     float4 *d4 = reinterpret_cast<float4 *>(dst);
@@ -111,40 +141,65 @@ __device__ __forceinline__ void store_row_smem(float *dst, const double (&a)[64]
         d4[i] = make_float4((float)a[4 * i], (float)a[4 * i + 1], (float)a[4 * i + 2], (float)a[4 * i + 3]);
 }
 
-template <bool WAVELETS>
-__global__ void __launch_bounds__(192) psyv_queries_kernel(const int32_t *__restrict__ rgb, int64_t nq,
-                                                            const PsyvTables *__restrict__ tabs,
-                                                            PsyvConsts K, const double *__restrict__ lut,
-                                                            const double *__restrict__ qw,
-                                                            float *__restrict__ out) {
+template <bool WAVELETS, bool LINEAR>
+__global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t *__restrict__ rgb, int64_t nq,
+                                                                   const PsyvTables *__restrict__ tabs,
+                                                                   PsyvConsts K, const double *__restrict__ lut,
+                                                                   const double *__restrict__ qw,
+                                                                   float *__restrict__ out, PsyvOperandOut op) {
     extern __shared__ __align__(16) uint8_t psm[];
-    PsyvTables &T = *reinterpret_cast<PsyvTables *>(psm);
-    int32_t *sin = reinterpret_cast<int32_t *>(psm + sizeof(PsyvTables));
-    float *sout = reinterpret_cast<float *>(sin + PQ_TILES * PQ_IN_STRIDE);
+    double *cpn = reinterpret_cast<double *>(psm);
+    double *ftab = reinterpret_cast<double *>(psm + PQ_CPN_BYTES);
+    float *sout = reinterpret_cast<float *>(psm);
     const int64_t q0 = (int64_t)blockIdx.x * PQ_TILES;
     const int ntile = (int)min((int64_t)PQ_TILES, nq - q0);
-    for (int i = threadIdx.x; i < (int)(sizeof(PsyvTables) / 8); i += blockDim.x)
-        reinterpret_cast<double *>(&T)[i] = reinterpret_cast<const double *>(tabs)[i];
-    {   // coalesced load of the block's tiles (16 int4 per tile)
-        const int4 *src = reinterpret_cast<const int4 *>(rgb + q0 * 64);
-        for (int e = threadIdx.x; e < ntile * 16; e += blockDim.x)
-            *reinterpret_cast<int4 *>(sin + (e >> 4) * PQ_IN_STRIDE + (e & 15) * 4) = __ldg(src + e);
+    if (!LINEAR) {
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) ftab[i] = tabs->f[i];
+        __syncthreads();
+    }
+    {   // pixel phase (FromRGB main.pas:571-576, RGBToYUV main.pas:2662-2677); all of a thread's pixels are
+        // requested before the first one is used (22 independent loads in flight per thread)
+        const int32_t *src = rgb + q0 * 64;
+        constexpr int PER_THREAD = (PQ_TILES * 64 + PQ_THREADS - 1) / PQ_THREADS;
+        int32_t colv[PER_THREAD];
+#pragma unroll
+        for (int k = 0; k < PER_THREAD; k++) {
+            const int e = threadIdx.x + k * PQ_THREADS;
+            colv[k] = e < ntile * 64 ? __ldg(src + e) : 0;
+        }
+#pragma unroll
+        for (int k = 0; k < PER_THREAD; k++) {
+            const int e = threadIdx.x + k * PQ_THREADS;
+            if (e < ntile * 64) {
+                const int32_t col = colv[k];
+                const double fr = channel_value<LINEAR>(col & 0xff, ftab, K.rcp255);
+                const double fg = channel_value<LINEAR>((col >> 8) & 0xff, ftab, K.rcp255);
+                const double fb = channel_value<LINEAR>((col >> 16) & 0xff, ftab, K.rcp255);
+                const double x = (2126.0 * fr + 7152.0 * fg) + 722.0 * fb;
+                const double qd = x * K.luma_rcp; // x / cLumaDiv, see plane_value
+                const double y = fma(fma(-qd, K.luma_div, x), K.luma_rcp, qd);
+                double *dst = cpn + (e >> 6) * PQ_CPN_STRIDE + (e & 63);
+                dst[0] = y;
+                dst[PQ_TILES * PQ_CPN_STRIDE] = (fb - y) * K.cu;
+                dst[2 * PQ_TILES * PQ_CPN_STRIDE] = (fr - y) * K.cv;
+            }
+        }
     }
     __syncthreads();
-    // lanes of a warp take consecutive tiles of ONE plane so the plane branch is warp-uniform
-    // (192 threads = 3 planes x 64 tiles)
-    const int plane = threadIdx.x / 64, tl = threadIdx.x & 63;
+    // lanes of a warp take consecutive tiles of ONE plane (96 threads = 3 planes x 32 tiles)
+    const int plane = threadIdx.x / PQ_TILES, tl = threadIdx.x % PQ_TILES;
+    double a[64];
     if (tl < ntile) {
-        const int4 *src = reinterpret_cast<const int4 *>(sin + tl * PQ_IN_STRIDE);
-        double a[64];
+        const double2 *src = reinterpret_cast<const double2 *>(cpn + (plane * PQ_TILES + tl) * PQ_CPN_STRIDE);
 #pragma unroll
-        for (int i = 0; i < 16; i++) {
-            const int4 v = src[i];
-            a[4 * i + 0] = plane_value(v.x, plane, &T, K);
-            a[4 * i + 1] = plane_value(v.y, plane, &T, K);
-            a[4 * i + 2] = plane_value(v.z, plane, &T, K);
-            a[4 * i + 3] = plane_value(v.w, plane, &T, K);
+        for (int i = 0; i < 32; i++) {
+            const double2 v = src[i];
+            a[2 * i] = v.x;
+            a[2 * i + 1] = v.y;
         }
+    }
+    __syncthreads(); // every component row is in registers: the buffer becomes the output staging
+    if (tl < ntile) {
         float *dst = sout + tl * PQ_OUT_STRIDE + plane * 64;
         if (WAVELETS) {
             haar_level<8>(a, K.haar);
@@ -158,9 +213,44 @@ __global__ void __launch_bounds__(192) psyv_queries_kernel(const int32_t *__rest
     __syncthreads();
     {   // coalesced store of the block's rows (48 float4 per row)
         float4 *dst = reinterpret_cast<float4 *>(out + q0 * TM_DCT);
-        for (int e = threadIdx.x; e < ntile * 48; e += blockDim.x) {
+        for (int e = threadIdx.x; e < ntile * 48; e += PQ_THREADS) {
             const int t = e / 48, j = e - t * 48;
             dst[e] = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + j * 4);
+        }
+    }
+    if (op.q16) { // 16 lanes per row, 3 float4 each; six rows per pass (trip count uniform: shuffles need full warps)
+        const int l16 = threadIdx.x & 15, grp = threadIdx.x >> 4;
+        const float4 *mean4 = reinterpret_cast<const float4 *>(op.mean);
+#pragma unroll 1
+        for (int i = 0; i < (PQ_TILES + 5) / 6; i++) {
+            const int t = grp + 6 * i;
+            float s16 = 0.f, sex = 0.f;
+            if (t < ntile) {
+                uint2 *drow = reinterpret_cast<uint2 *>(op.q16 + (q0 + t) * TM_DCT);
+#pragma unroll
+                for (int c = l16; c < 48; c += 16) {
+                    const float4 x = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + c * 4);
+                    const float4 m = __ldg(mean4 + c);
+                    const float v0 = x.x - m.x, v1 = x.y - m.y, v2 = x.z - m.z, v3 = x.w - m.w;
+                    const __half2 h01 = __floats2half2_rn(v0, v1), h23 = __floats2half2_rn(v2, v3);
+                    const float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
+                    s16 += f01.x * f01.x; s16 += f01.y * f01.y; s16 += f23.x * f23.x; s16 += f23.y * f23.y;
+                    sex += v0 * v0; sex += v1 * v1; sex += v2 * v2; sex += v3 * v3;
+                    uint2 pk;
+                    pk.x = *reinterpret_cast<const unsigned int *>(&h01);
+                    pk.y = *reinterpret_cast<const unsigned int *>(&h23);
+                    drow[c] = pk;
+                }
+            }
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                s16 += __shfl_xor_sync(0xffffffffu, s16, o);
+                sex += __shfl_xor_sync(0xffffffffu, sex, o);
+            }
+            if (t < ntile && l16 == 0) {
+                op.qn16[q0 + t] = s16;
+                op.qne[q0 + t] = sqrtf(sex);
+            }
         }
     }
 }
@@ -379,6 +469,7 @@ struct PsyvDeviceState {
     double *lut = nullptr;                            // 4096 DCT lut + 64 cUVRatio
     double *qw = nullptr;                             // 192 Q weights
     int device = -1;
+    bool linear_ok = false; // the arithmetic c / 255.0 matched the table for all 256 values
     std::mutex mu;
 } g_ps;
 
@@ -397,6 +488,15 @@ int ensure_tables() {
     TM_CUDA(cudaGetDevice(&dev));
     if (g_ps.device == dev && g_ps.lut) return 0;
     static const double gam[2] = {2.0, 0.6}; // main.pas:586
+    {   // the kernels' table-free evaluation of c / 255.0 (channel_value), replayed on the host
+        const double rcp = 1.0 / 255.0;
+        bool ok = true;
+        for (int c = 0; c < 256; c++) {
+            const double cd = (double)c, q0 = cd * rcp;
+            ok = ok && std::fma(std::fma(-q0, 255.0, cd), rcp, q0) == c / 255.0;
+        }
+        g_ps.linear_ok = ok;
+    }
     for (int g = -1; g < 2; g++) {
         PsyvTables *h = new PsyvTables;
         for (int c = 0; c < 256; c++) {
@@ -443,6 +543,7 @@ PsyvConsts make_consts() {
     K.luma_div = luma;
     K.luma_rcp = 1.0 / luma;
     K.haar = 1.0 / sqrt(2.0);
+    K.rcp255 = 1.0 / 255.0;
     return K;
 }
 
@@ -450,23 +551,38 @@ PsyvConsts make_consts() {
 
 int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
                            cudaStream_t s) {
+    return tm_launch_psyv_queries_operand(d_rgb, nq, flags, gamma, d_out, nullptr, nullptr, nullptr, nullptr, s);
+}
+
+int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
+                                   const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, cudaStream_t s) {
     if (gamma < -1 || gamma > 1) { tm_set_error("gamma must be -1, 0 or 1"); return TM_EINVAL; }
     if (nq == 0) return 0;
     int r = ensure_tables();
     if (r) return r;
     PsyvConsts K = make_consts();
-    unsigned grid = (unsigned)((nq + 63) / 64);
+    unsigned grid = (unsigned)((nq + PQ_TILES - 1) / PQ_TILES);
     const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
     static bool attr = false;
     if (!attr) {
-        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM));
-        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
         attr = true;
     }
-    if (flags & TM_PSYV_WAVELETS)
-        psyv_queries_kernel<true><<<grid, 192, PQ_SMEM, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+    const bool linear = gamma < 0 && g_ps.linear_ok; // GammaCor = -1: c / 255.0 without the table
+    const bool wav = (flags & TM_PSYV_WAVELETS) != 0;
+    const PsyvTables *tabs = g_ps.tabs[gamma + 1];
+    const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne};
+    if (wav && linear)
+        psyv_queries_kernel<true, true><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+    else if (wav)
+        psyv_queries_kernel<true, false><<<grid, PQ_THREADS, PQ_SMEM_LUT, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+    else if (linear)
+        psyv_queries_kernel<false, true><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     else
-        psyv_queries_kernel<false><<<grid, 192, PQ_SMEM, s>>>(d_rgb, nq, g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_out);
+        psyv_queries_kernel<false, false><<<grid, PQ_THREADS, PQ_SMEM_LUT, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "psyv_queries_kernel");
 }

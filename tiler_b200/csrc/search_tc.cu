@@ -271,7 +271,36 @@ int ensure_tc_scratch(int64_t nq_pad, int kp, size_t cand_elems, cudaStream_t s)
 }
 } // namespace
 
+static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s,
+                          bool operand_ready);
+
 int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s) {
+    return search_tc_impl(h, d_q, nq, k, d_idx, d_err, s, false);
+}
+
+int tm_search_tc_prepared(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s) {
+    return search_tc_impl(h, d_q, nq, k, d_idx, d_err, s, true);
+}
+
+int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **d_qn16, float **d_qne, cudaStream_t s) {
+    if (!h->rows_f16 || h->kp != h->dd || nq < 1) return 1; // fused operand rows are unpadded: kp == dd only
+    const int64_t nq_pad = ((nq + TC_QTILE - 1) / TC_QTILE) * TC_QTILE;
+    std::lock_guard<std::mutex> lk(g_tc.mu);
+    int r = ensure_tc_scratch(nq_pad, h->kp, 0, s);
+    if (r) return r;
+    if (nq_pad > nq) { // zero operand and norms for the padding queries, as operand_kernel writes them
+        TM_CUDA(cudaMemsetAsync(g_tc.q16 + (size_t)nq * h->kp, 0, sizeof(__half) * (size_t)(nq_pad - nq) * h->kp, s));
+        TM_CUDA(cudaMemsetAsync(g_tc.qn16 + nq, 0, sizeof(float) * (size_t)(nq_pad - nq), s));
+        TM_CUDA(cudaMemsetAsync(g_tc.qne + nq, 0, sizeof(float) * (size_t)(nq_pad - nq), s));
+    }
+    *d_q16 = g_tc.q16;
+    *d_qn16 = g_tc.qn16;
+    *d_qne = g_tc.qne;
+    return 0;
+}
+
+static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s,
+                          bool operand_ready) {
     if (!h->rows_f16 || k > 8 || ((uintptr_t)d_q & 15)) // outside the tensor-core path's envelope: exact engine
         return tm_launch_search_simt(h->rows_f32, h->n, h->dd, d_q, nq, k, d_idx, d_err, s);
     const int kc = (k <= 4) ? 8 : 16;
@@ -297,7 +326,7 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
     std::lock_guard<std::mutex> lk(g_tc.mu);
     int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)nq_pad * nlists * kc, s);
     if (r) return r;
-    if ((r = tm_launch_query_operand(h, d_q, nq, nq_pad, g_tc.q16, g_tc.qn16, g_tc.qne, s))) return r;
+    if (!operand_ready && (r = tm_launch_query_operand(h, d_q, nq, nq_pad, g_tc.q16, g_tc.qn16, g_tc.qne, s))) return r;
     CUtensorMap tq;
     if ((r = make_tmap(&tq, g_tc.q16, nq_pad, h->kp))) return r;
     const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
