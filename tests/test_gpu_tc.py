@@ -88,3 +88,29 @@ def test_tc_out_of_fp16_range_falls_back_to_exact(tb, oracle):
         ti, te = t.search_batch(q, k=1)
     oi, od = oracle.knn_f32(ds, q, 1)
     assert np.array_equal(ti, oi) and np.array_equal(te, od)
+
+
+@pytest.mark.parametrize("layout", ["interleaved", "contiguous"])
+def test_tc_second_chance_for_rejected_queries(tb, oracle, layout):
+    """Clusters of 40 near-identical rows: with k = 8 more rows sit inside the certificate's band than a
+    16-entry list holds, so the first pass rejects the queries.  Interleaved clusters spread over the 16
+    lists of the finest row split (second tensor-core pass certifies them); contiguous clusters overflow
+    there too and end on the exact engine.  Either way the result is the exact engine's, bit for bit."""
+    rng = np.random.default_rng(17)
+    nbase, rep = 3200, 40                      # 128 000 rows
+    base = rng.standard_normal((nbase, 192)).astype(np.float32)
+    jit = (1e-4 * rng.standard_normal((rep, nbase, 192))).astype(np.float32)
+    ds = base[None] + jit                      # [rep][nbase][192]
+    ds = ds.reshape(-1, 192) if layout == "interleaved" else ds.transpose(1, 0, 2).reshape(-1, 192)
+    ds = np.ascontiguousarray(ds)
+    q = base[:2304] + (1e-3 * rng.standard_normal((2304, 192))).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        si, se, ti, te, st = _both(tb, t, q, 8)
+    assert np.array_equal(se.view(np.uint32), te.view(np.uint32))
+    assert np.array_equal(si, ti)
+    if layout == "interleaved":
+        assert st["fallback_queries"] < 100, st   # certified on the second pass
+    else:
+        assert st["fallback_queries"] > 2000, st  # 40 rows of one cluster in one list: exact engine
+    oi, od = oracle.knn_f32(ds, q[:64], 8)
+    assert np.array_equal(te[:64].view(np.uint32), od.view(np.uint32))

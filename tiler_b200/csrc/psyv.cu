@@ -122,6 +122,7 @@ struct PsyvOperandOut {
     __half *q16;       // [nq][192]
     float *qn16;       // sum of squares of the rounded values
     float *qne;        // Euclidean norm of the centred float row
+    float *qde;        // Euclidean norm of the fp16 rounding error of the centred row
 };
 
 template <bool LINEAR>
@@ -224,7 +225,7 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
 #pragma unroll 1
         for (int i = 0; i < (PQ_TILES + 5) / 6; i++) {
             const int t = grp + 6 * i;
-            float s16 = 0.f, sex = 0.f;
+            float s16 = 0.f, sex = 0.f, sde = 0.f;
             if (t < ntile) {
                 uint2 *drow = reinterpret_cast<uint2 *>(op.q16 + (q0 + t) * TM_DCT);
 #pragma unroll
@@ -236,6 +237,8 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
                     const float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
                     s16 += f01.x * f01.x; s16 += f01.y * f01.y; s16 += f23.x * f23.x; s16 += f23.y * f23.y;
                     sex += v0 * v0; sex += v1 * v1; sex += v2 * v2; sex += v3 * v3;
+                    const float e0 = v0 - f01.x, e1 = v1 - f01.y, e2 = v2 - f23.x, e3 = v3 - f23.y; // exact
+                    sde += e0 * e0; sde += e1 * e1; sde += e2 * e2; sde += e3 * e3;
                     uint2 pk;
                     pk.x = *reinterpret_cast<const unsigned int *>(&h01);
                     pk.y = *reinterpret_cast<const unsigned int *>(&h23);
@@ -246,10 +249,12 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
             for (int o = 8; o > 0; o >>= 1) {
                 s16 += __shfl_xor_sync(0xffffffffu, s16, o);
                 sex += __shfl_xor_sync(0xffffffffu, sex, o);
+                sde += __shfl_xor_sync(0xffffffffu, sde, o);
             }
             if (t < ntile && l16 == 0) {
                 op.qn16[q0 + t] = s16;
                 op.qne[q0 + t] = sqrtf(sex);
+                op.qde[q0 + t] = sqrtf(sde);
             }
         }
     }
@@ -551,11 +556,12 @@ PsyvConsts make_consts() {
 
 int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
                            cudaStream_t s) {
-    return tm_launch_psyv_queries_operand(d_rgb, nq, flags, gamma, d_out, nullptr, nullptr, nullptr, nullptr, s);
+    return tm_launch_psyv_queries_operand(d_rgb, nq, flags, gamma, d_out, nullptr, nullptr, nullptr, nullptr, nullptr, s);
 }
 
 int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
-                                   const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, cudaStream_t s) {
+                                   const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, float *d_qde,
+                                   cudaStream_t s) {
     if (gamma < -1 || gamma > 1) { tm_set_error("gamma must be -1, 0 or 1"); return TM_EINVAL; }
     if (nq == 0) return 0;
     int r = ensure_tables();
@@ -574,7 +580,7 @@ int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, 
     const bool linear = gamma < 0 && g_ps.linear_ok; // GammaCor = -1: c / 255.0 without the table
     const bool wav = (flags & TM_PSYV_WAVELETS) != 0;
     const PsyvTables *tabs = g_ps.tabs[gamma + 1];
-    const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne};
+    const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne, d_qde};
     if (wav && linear)
         psyv_queries_kernel<true, true><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     else if (wav)

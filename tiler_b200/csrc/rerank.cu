@@ -8,7 +8,8 @@
 namespace {
 
 constexpr int RR_THREADS = 128; // one thread per query
-constexpr int RR_MAXV = 64;     // candidates below the final threshold a query may carry (more -> exact engine)
+constexpr int RR_MAXV = 64;     // candidates below the final threshold a query may carry (more -> rejected) ...
+constexpr int RR_MAXV_WIDE = 192; // ... when the lists hold more than 64 slots (finest row split, k > 4)
 constexpr int RR_K = 8;         // the tensor-core path serves k <= 8
 
 // exact float32 squared distance, one sequential add chain in dimension order, no FMA (-fmad=false):
@@ -49,9 +50,11 @@ template <bool K1, bool STAGED>
 __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     const float *__restrict__ rows, int dd, const float *__restrict__ q, int64_t nq,
     const float *__restrict__ cand_s, const int *__restrict__ cand_i, const float *__restrict__ cand_tau, int nlists, int kc,
-    const float *__restrict__ qn16, const float *__restrict__ qne, float max_tnorm, int k,
+    const float *__restrict__ qn16, const float *__restrict__ qne, const float *__restrict__ qde, float max_tnorm,
+    float max_dnorm, int k, int maxv,
     int *__restrict__ idx, float *__restrict__ err, int *__restrict__ fb_list, int *__restrict__ fb_count) {
-    __shared__ uint8_t vlist[RR_MAXV][RR_THREADS]; // slot positions (< nlists * kc <= 256) of the live candidates
+    extern __shared__ uint8_t vlist_dyn[]; // [maxv][RR_THREADS] slot positions (< nlists * kc <= 256) of the live candidates
+    uint8_t (*vlist)[RR_THREADS] = reinterpret_cast<uint8_t (*)[RR_THREADS]>(vlist_dyn);
     __shared__ __align__(16) float seg[STAGED ? RR_THREADS / 32 : 1][2][32 * RR_SEG_STRIDE];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int64_t qg = (int64_t)blockIdx.x * RR_THREADS + threadIdx.x;
@@ -75,11 +78,11 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
 #pragma unroll
             for (int e = 0; e < 4; e++)
                 if (r[e] >= 0 && (s[e] < tau || !(tau < INFINITY))) {
-                    if (cnt < RR_MAXV) vlist[cnt][threadIdx.x] = (uint8_t)(c4 * 4 + e); else overflow = true;
+                    if (cnt < maxv) vlist[cnt][threadIdx.x] = (uint8_t)(c4 * 4 + e); else overflow = true;
                     cnt++;
                 }
         }
-        if (cnt > RR_MAXV) cnt = RR_MAXV;
+        if (cnt > maxv) cnt = maxv;
     }
     float bd[K1 ? 1 : RR_K];
     int bi[K1 ? 1 : RR_K];
@@ -157,9 +160,11 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     // NaN / overflowed fp16 query operands never certify (their scores are NaN and select nothing).
     bool ok = !overflow && qn16[qg] < 3.0e38f;
     if (ok && tau < INFINITY) {
-        const double nsum = (double)qne[qg] + (double)max_tnorm;
-        const double a = 6e-5 * nsum * nsum + 1e-6;                   // fp32 accumulation slack
-        const double e = nsum * (1.001 / 2048.0) + 1e-6;              // fp16 rounding of both vectors
+        const float nsumf = qne[qg] + max_tnorm;
+        const double nsum = (double)nsumf;
+        const double a = (double)tc_band_a(nsumf);                        // fp32 accumulation slack (search_tc.h)
+        const double e = (double)tc_band_e(qde[qg], max_dnorm, nsumf);    // fp16 rounding of both vectors
+        (void)nsum;
         const double dt = (double)tau + (double)qn16[qg] - a;
         double root = sqrt(dt > 0.0 ? dt : 0.0) - e;
         if (root < 0.0) root = 0.0;
@@ -173,11 +178,22 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
 
 int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, const float *d_cand_s,
                      const int *d_cand_i, const float *d_cand_tau, int nsplit, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
-                     float max_tnorm, int k, int *d_idx, float *d_err, int *d_fb_list, int *d_fb_count,
+                     const float *d_qdnorm, float max_tnorm, float max_dnorm, int k, int *d_idx, float *d_err, int *d_fb_list, int *d_fb_count,
                      cudaStream_t s) {
     const unsigned grid = (unsigned)((nq + RR_THREADS - 1) / RR_THREADS);
     const bool staged = (dd & 3) == 0 && (((uintptr_t)d_q | (uintptr_t)d_rows) & 15) == 0;
-#define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, 0, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, max_tnorm, k, d_idx, d_err, d_fb_list, d_fb_count)
+    const int maxv = nsplit * kc > RR_MAXV ? RR_MAXV_WIDE : RR_MAXV;
+    const size_t dyn = (size_t)maxv * RR_THREADS;
+    static bool attr = false;
+    if (!attr) {
+        const int wide = RR_MAXV_WIDE * RR_THREADS;
+        TM_CUDA(cudaFuncSetAttribute(rerank_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
+        TM_CUDA(cudaFuncSetAttribute(rerank_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
+        TM_CUDA(cudaFuncSetAttribute(rerank_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
+        TM_CUDA(cudaFuncSetAttribute(rerank_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
+        attr = true;
+    }
+#define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, dyn, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, d_qdnorm, max_tnorm, max_dnorm, k, maxv, d_idx, d_err, d_fb_list, d_fb_count)
     if (k == 1) { if (staged) RR_LAUNCH(true, true); else RR_LAUNCH(true, false); }
     else { if (staged) RR_LAUNCH(false, true); else RR_LAUNCH(false, false); }
 #undef RR_LAUNCH

@@ -54,13 +54,14 @@ __global__ void colmean_final_kernel(const double *__restrict__ part, int nblock
 // values, what the GEMM sees), exact-ish ||t'|| for the slack, range check for fp16
 __global__ void operand_kernel(const float *__restrict__ rows, int64_t n, int64_t n_pad, int dd, int kp,
                                const float *__restrict__ mean, __half *__restrict__ out16,
-                               float *__restrict__ norm16, float *__restrict__ norm_exact, float pad_norm,
+                               float *__restrict__ norm16, float *__restrict__ norm_exact,
+                               float *__restrict__ dnorm, float pad_norm,
                                float out_scale, unsigned int *__restrict__ max_norm_bits,
                                unsigned int *__restrict__ max_abs_bits) {
     int64_t r = (int64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x / 32);
     int lane = threadIdx.x & 31;
     if (r >= n_pad) return;
-    float s16 = 0.f, sex = 0.f, mabs = 0.f;
+    float s16 = 0.f, sex = 0.f, sde = 0.f, mabs = 0.f;
     for (int j = lane; j < kp; j += 32) {
         float v = 0.f;
         if (r < n && j < dd) v = rows[r * dd + j] - mean[j];
@@ -69,22 +70,26 @@ __global__ void operand_kernel(const float *__restrict__ rows, int64_t n, int64_
         out16[r * kp + j] = __float2half_rn(out_scale * hv); // out_scale is a power of two: exact
         s16 += hv * hv;
         sex += v * v;
+        sde += (v - hv) * (v - hv); // v - hv is exact in fp32
         mabs = fmaxf(mabs, fabsf(v));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         s16 += __shfl_xor_sync(0xffffffffu, s16, o);
         sex += __shfl_xor_sync(0xffffffffu, sex, o);
+        sde += __shfl_xor_sync(0xffffffffu, sde, o);
         mabs = fmaxf(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
     }
     if (lane == 0) {
         norm16[r] = (r < n) ? s16 : pad_norm;
         if (norm_exact) norm_exact[r] = sqrtf(sex);
+        if (dnorm) dnorm[r] = sqrtf(sde);
         if (r < n) {
             if (max_norm_bits) atomicMax(max_norm_bits, __float_as_uint(sqrtf(sex)));
             if (max_abs_bits) {
                 atomicMax(max_abs_bits, __float_as_uint(mabs));
                 atomicMax(max_abs_bits + 1, __float_as_uint(s16));
+                atomicMax(max_abs_bits + 2, __float_as_uint(sqrtf(sde)));
             }
         }
     }
@@ -172,18 +177,18 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     unsigned int *mx = nullptr;
     __half *r16 = nullptr;
     TM_CUDA(cudaMalloc(&part, sizeof(double) * (size_t)nblocks * h->dd));
-    TM_CUDA(cudaMalloc(&mx, 3 * sizeof(unsigned int)));
+    TM_CUDA(cudaMalloc(&mx, 4 * sizeof(unsigned int)));
     TM_CUDA(cudaMalloc(&h->mean, sizeof(float) * h->dd));
     TM_CUDA(cudaMalloc(&h->norms, sizeof(float) * n_pad));
     TM_CUDA(cudaMalloc(&r16, sizeof(__half) * (size_t)n_pad * kp));
-    TM_CUDA(cudaMemsetAsync(mx, 0, 3 * sizeof(unsigned int), s));
+    TM_CUDA(cudaMemsetAsync(mx, 0, 4 * sizeof(unsigned int), s));
     colsum_partial_kernel<<<nblocks, 192, 0, s>>>(h->rows_f32, h->n, h->dd, part);
     colmean_final_kernel<<<(h->dd + 63) / 64, 64, 0, s>>>(part, nblocks, h->n, h->dd, h->mean);
     operand_kernel<<<(unsigned)((n_pad + 7) / 8), 256, 0, s>>>(h->rows_f32, h->n, n_pad, h->dd, kp, h->mean, r16,
-                                                             h->norms, nullptr, INFINITY, -2.f, mx, mx + 1);
+                                                             h->norms, nullptr, nullptr, INFINITY, -2.f, mx, mx + 1);
     tm_count_launch(3);
     TM_CUDA(cudaGetLastError());
-    unsigned int hmx[3];
+    unsigned int hmx[4];
     TM_CUDA(cudaMemcpyAsync(hmx, mx, sizeof hmx, cudaMemcpyDeviceToHost, s));
     TM_CUDA(cudaStreamSynchronize(s));
     cudaFree(part);
@@ -209,6 +214,7 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     h->n_pad = n_pad;
     h->kp = kp;
     h->max_norm = max_norm;
+    memcpy(&h->max_dnorm, &hmx[3], 4);
     h->tmap_rows = malloc(2 * sizeof(CUtensorMap)); // [0] rows_f16, [1] norm tiles
     int r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows), r16, n_pad, kp);
     if (!r) r = make_tmap_norm(static_cast<CUtensorMap *>(h->tmap_rows) + 1, h->norm_tiles, n_pad / 128);
@@ -216,9 +222,9 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
 }
 
 int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, int64_t nq_pad, __half *d_q16,
-                            float *d_qnorm16, float *d_qnorm_exact, cudaStream_t s) {
+                            float *d_qnorm16, float *d_qnorm_exact, float *d_qdnorm, cudaStream_t s) {
     operand_kernel<<<(unsigned)((nq_pad + 7) / 8), 256, 0, s>>>(d_q, nq, nq_pad, h->dd, h->kp, h->mean, d_q16,
-                                                              d_qnorm16, d_qnorm_exact, 0.f, 1.f, nullptr, nullptr);
+                                                              d_qnorm16, d_qnorm_exact, d_qdnorm, 0.f, 1.f, nullptr, nullptr);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "operand_kernel(q)");
 }
@@ -234,7 +240,7 @@ int tm_make_query_tmap(void *tmap, const __half *d_q16, int64_t nq_pad, int kp) 
 namespace {
 struct TcScratch {
     __half *q16 = nullptr;
-    float *qn16 = nullptr, *qne = nullptr, *cand_s = nullptr, *cand_tau = nullptr;
+    float *qn16 = nullptr, *qne = nullptr, *qde = nullptr, *cand_s = nullptr, *cand_tau = nullptr;
     int *cand_i = nullptr, *fb_list = nullptr, *fb_count = nullptr;
     int *h_count = nullptr; // pinned
     size_t cap_q = 0, cap_c = 0;
@@ -245,11 +251,12 @@ struct TcScratch {
 int ensure_tc_scratch(int64_t nq_pad, int kp, size_t cand_elems, cudaStream_t s) {
     if ((size_t)nq_pad * kp > g_tc.cap_q * (size_t)(g_tc.kp ? g_tc.kp : 1) || kp != g_tc.kp || (size_t)nq_pad > g_tc.cap_q) {
         cudaStreamSynchronize(s);
-        cudaFree(g_tc.q16); cudaFree(g_tc.qn16); cudaFree(g_tc.qne); cudaFree(g_tc.fb_list);
+        cudaFree(g_tc.q16); cudaFree(g_tc.qn16); cudaFree(g_tc.qne); cudaFree(g_tc.qde); cudaFree(g_tc.fb_list);
         g_tc.q16 = nullptr; g_tc.cap_q = 0;
         TM_CUDA(cudaMalloc(&g_tc.q16, sizeof(__half) * (size_t)nq_pad * kp));
         TM_CUDA(cudaMalloc(&g_tc.qn16, sizeof(float) * nq_pad));
         TM_CUDA(cudaMalloc(&g_tc.qne, sizeof(float) * nq_pad));
+        TM_CUDA(cudaMalloc(&g_tc.qde, sizeof(float) * nq_pad));
         TM_CUDA(cudaMalloc(&g_tc.fb_list, sizeof(int) * nq_pad));
         g_tc.cap_q = nq_pad;
         g_tc.kp = kp;
@@ -282,7 +289,8 @@ int tm_search_tc_prepared(ANNkdtree *h, const float *d_q, int64_t nq, int k, int
     return search_tc_impl(h, d_q, nq, k, d_idx, d_err, s, true);
 }
 
-int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **d_qn16, float **d_qne, cudaStream_t s) {
+int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **d_qn16, float **d_qne, float **d_qde,
+                                cudaStream_t s) {
     if (!h->rows_f16 || h->kp != h->dd || nq < 1) return 1; // fused operand rows are unpadded: kp == dd only
     const int64_t nq_pad = ((nq + TC_QTILE - 1) / TC_QTILE) * TC_QTILE;
     std::lock_guard<std::mutex> lk(g_tc.mu);
@@ -292,17 +300,21 @@ int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **
         TM_CUDA(cudaMemsetAsync(g_tc.q16 + (size_t)nq * h->kp, 0, sizeof(__half) * (size_t)(nq_pad - nq) * h->kp, s));
         TM_CUDA(cudaMemsetAsync(g_tc.qn16 + nq, 0, sizeof(float) * (size_t)(nq_pad - nq), s));
         TM_CUDA(cudaMemsetAsync(g_tc.qne + nq, 0, sizeof(float) * (size_t)(nq_pad - nq), s));
+        TM_CUDA(cudaMemsetAsync(g_tc.qde + nq, 0, sizeof(float) * (size_t)(nq_pad - nq), s));
     }
     *d_q16 = g_tc.q16;
     *d_qn16 = g_tc.qn16;
     *d_qne = g_tc.qne;
+    *d_qde = g_tc.qde;
     return 0;
 }
 
-static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s,
-                          bool operand_ready) {
-    if (!h->rows_f16 || k > 8 || ((uintptr_t)d_q & 15)) // outside the tensor-core path's envelope: exact engine
-        return tm_launch_search_simt(h->rows_f32, h->n, h->dd, d_q, nq, k, d_idx, d_err, s);
+// One coarse pass + re-rank over a query batch.  Queries the certificate rejects are listed in g_tc.fb_list;
+// their number is returned through *nfb_out (one host round trip).  finest_split: use the largest row split
+// (most candidate lists per query) regardless of the batch size - the second chance for rejected queries.
+// Caller holds g_tc.mu.
+static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s,
+                   bool operand_ready, bool finest_split, int *nfb_out, int *nlists_out) {
     const int kc = (k <= 4) ? 8 : 16;
     const int nch = h->kp / 64;
     const int64_t nq_pad = ((nq + TC_QTILE - 1) / TC_QTILE) * TC_QTILE;
@@ -316,24 +328,25 @@ static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int
     int nsplit = 1;
     const int want = pair ? 4 * tm_num_sms() : 8 * tm_num_sms();
     if (qblocks < want) nsplit = (want + qblocks - 1) / qblocks;
+    if (finest_split) nsplit = pair ? 8 : 16;
     if (nsplit > total_tiles / 4) nsplit = total_tiles / 4;
     if (nsplit > (pair ? 8 : 16)) nsplit = pair ? 8 : 16;
     if (nsplit < 1) nsplit = 1;
     int tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
     nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
     const int nlists = pair ? 2 * nsplit : nsplit;
+    *nlists_out = nlists;
 
-    std::lock_guard<std::mutex> lk(g_tc.mu);
     int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)nq_pad * nlists * kc, s);
     if (r) return r;
-    if (!operand_ready && (r = tm_launch_query_operand(h, d_q, nq, nq_pad, g_tc.q16, g_tc.qn16, g_tc.qne, s))) return r;
+    if (!operand_ready && (r = tm_launch_query_operand(h, d_q, nq, nq_pad, g_tc.q16, g_tc.qn16, g_tc.qne, g_tc.qde, s))) return r;
     CUtensorMap tq;
     if ((r = make_tmap(&tq, g_tc.q16, nq_pad, h->kp))) return r;
     const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
     const CUtensorMap &tn = static_cast<const CUtensorMap *>(h->tmap_rows)[1];
     TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
     int tok = tm_prof_begin(2, s);
-#define TC_ARGS qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, h->max_norm, k, s
+#define TC_ARGS qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, g_tc.qde, h->max_norm, h->max_dnorm, k, s
 #define TC_LAUNCH(NCH, KC, K1) (pair ? launch_tc2<NCH, KC, K1>(tq, tt, tn, h->norm_scale, TC_ARGS) \
                                      : launch_tc<NCH, KC, K1>(tq, tt, h->norm_tiles, h->norm_scale, TC_ARGS))
     if (k == 1) r = nch == 1 ? TC_LAUNCH(1, 8, true) : nch == 2 ? TC_LAUNCH(2, 8, true) : TC_LAUNCH(3, 8, true);
@@ -345,16 +358,90 @@ static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int
     if (r) return r;
     tok = tm_prof_begin(3, s);
     r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, nlists, kc, g_tc.qn16, g_tc.qne,
-                         h->max_norm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
+                         g_tc.qde, h->max_norm, h->max_dnorm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
     tm_prof_end(tok, s);
     if (r) return r;
-    // queries the certificate rejected go through the exact engine (one host round trip for the count)
     TM_CUDA(cudaMemcpyAsync(g_tc.h_count, g_tc.fb_count, sizeof(int), cudaMemcpyDeviceToHost, s));
     TM_CUDA(cudaStreamSynchronize(s));
-    const int nfb = *g_tc.h_count;
-    if (nfb > 0) {
+    *nfb_out = *g_tc.h_count;
+    return 0;
+}
+
+namespace {
+__global__ void gather_rows_kernel(const float *__restrict__ q, const int *__restrict__ list, int n, int dd,
+                                   float *__restrict__ out) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; // one float4 each (dd % 4 == 0)
+    const int per = dd >> 2;
+    if (e >= (int64_t)n * per) return;
+    const int i = (int)(e / per), j = (int)(e - (int64_t)i * per);
+    reinterpret_cast<float4 *>(out)[e] = __ldg(reinterpret_cast<const float4 *>(q + (int64_t)list[i] * dd) + j);
+}
+
+__global__ void scatter_results_kernel(const int *__restrict__ list, int n, int k, const int *__restrict__ ti,
+                                       const float *__restrict__ te, int *__restrict__ idx, float *__restrict__ err) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n * k) return;
+    const int i = e / k, j = e - i * k;
+    idx[(int64_t)list[i] * k + j] = ti[e];
+    err[(int64_t)list[i] * k + j] = te[e];
+}
+} // namespace
+
+static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s,
+                          bool operand_ready) {
+    if (!h->rows_f16 || k > 8 || ((uintptr_t)d_q & 15)) // outside the tensor-core path's envelope: exact engine
+        return tm_launch_search_simt(h->rows_f32, h->n, h->dd, d_q, nq, k, d_idx, d_err, s);
+    std::lock_guard<std::mutex> lk(g_tc.mu);
+    int nfb = 0, nlists0 = 0, nlists1 = 0;
+    int r = tc_core(h, d_q, nq, k, d_idx, d_err, s, operand_ready, false, &nfb, &nlists0);
+    if (r || nfb == 0) return r;
+    static const bool trace = getenv("TM_TRACE") != nullptr;
+    if (trace) fprintf(stderr, "[tmann] tc pass 1: %d of %lld queries rejected (%d lists)\n", nfb, (long long)nq, nlists0);
+    // Rejected queries (candidate list too short for the rows inside the certificate's band, or an fp16
+    // overflow).  Second chance on the tensor cores with the finest row split - 16 lists per query instead of
+    // 2 - on a compacted copy of those queries; what is still rejected goes to the exact engine.  Worth it when
+    // the exact scan of the rejects would cost more than a short tensor-core pass.
+    const int finest = 16; // lists per query at the finest split (both kernels)
+    const bool retry = (h->dd & 3) == 0 && nfb >= 64 && (double)nfb * (double)h->n >= 2.5e8 && nlists0 < finest &&
+                       h->n_pad / 256 >= 32;
+    if (!retry) {
         g_fallbacks.fetch_add(nfb, std::memory_order_relaxed);
-        r = tm_launch_search_simt_list(h->rows_f32, h->n, h->dd, d_q, g_tc.fb_list, nullptr, nfb, k, d_idx, d_err, s);
+        return tm_launch_search_simt_list(h->rows_f32, h->n, h->dd, d_q, g_tc.fb_list, nullptr, nfb, k, d_idx, d_err, s);
     }
+    int *list0 = nullptr, *ti = nullptr;
+    float *qt = nullptr, *te = nullptr;
+    auto cleanup = [&]() { cudaFree(list0); cudaFree(ti); cudaFree(qt); cudaFree(te); };
+    r = tm_check(cudaMalloc(&list0, sizeof(int) * (size_t)nfb), "cudaMalloc(retry list)");
+    if (!r) r = tm_check(cudaMalloc(&qt, sizeof(float) * (size_t)nfb * h->dd), "cudaMalloc(retry queries)");
+    if (!r) r = tm_check(cudaMalloc(&ti, sizeof(int) * (size_t)nfb * k), "cudaMalloc(retry idx)");
+    if (!r) r = tm_check(cudaMalloc(&te, sizeof(float) * (size_t)nfb * k), "cudaMalloc(retry err)");
+    if (r) { cleanup(); return r; }
+    cudaMemcpyAsync(list0, g_tc.fb_list, sizeof(int) * (size_t)nfb, cudaMemcpyDeviceToDevice, s);
+    {
+        const int64_t total = (int64_t)nfb * (h->dd >> 2);
+        gather_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_q, list0, nfb, h->dd, qt);
+        tm_count_launch();
+    }
+    int nfb2 = 0;
+    r = tc_core(h, qt, nfb, k, ti, te, s, false, true, &nfb2, &nlists1);
+    if (trace) {
+        fprintf(stderr, "[tmann] tc pass 2: %d of %d queries rejected (%d lists); first rejected queries of pass 1:", nfb2, nfb, nlists1);
+        int first[16];
+        const int nshow = nfb < 16 ? nfb : 16;
+        cudaMemcpy(first, list0, sizeof(int) * nshow, cudaMemcpyDeviceToHost);
+        for (int i = 0; i < nshow; i++) fprintf(stderr, " %d", first[i]);
+        fprintf(stderr, "\n");
+    }
+    if (!r && nfb2 > 0) {
+        g_fallbacks.fetch_add(nfb2, std::memory_order_relaxed);
+        r = tm_launch_search_simt_list(h->rows_f32, h->n, h->dd, qt, g_tc.fb_list, nullptr, nfb2, k, ti, te, s);
+    }
+    if (!r) {
+        scatter_results_kernel<<<(unsigned)(((int64_t)nfb * k + 255) / 256), 256, 0, s>>>(list0, nfb, k, ti, te, d_idx, d_err);
+        tm_count_launch();
+        r = tm_check(cudaGetLastError(), "scatter_results_kernel");
+        if (!r) r = tm_check(cudaStreamSynchronize(s), "sync(retry)"); // the temporaries are freed below
+    }
+    cleanup();
     return r;
 }

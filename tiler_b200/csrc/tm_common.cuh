@@ -31,6 +31,7 @@ struct ANNkdtree {
     int64_t n_pad;
     int kp;
     float max_norm;  // max ||t-mu||
+    float max_dnorm; // max ||(t-mu) - fp16(t-mu)||: the rows' share of the coarse pass's rounding error
     void *tmap_rows; // CUtensorMap (host copy) for rows_f16
     std::mutex *single_mu; // serialises the legacy one-query entry points' scratch
     float *h_pin;          // pinned scratch for the legacy one-query entry points
@@ -108,10 +109,12 @@ int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32
                                      cudaStream_t s);
 // query descriptors + (optionally) the tensor-core engine's query operand in one pass
 int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
-                                   const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, cudaStream_t s);
+                                   const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, float *d_qde,
+                                   cudaStream_t s);
 // tensor-core engine with a query operand supplied by the caller: tm_tc_query_operand_buffers hands out the engine's
 // scratch (padding rows cleared) or returns 1 when the engine does not apply to this (dataset, k, nq)
-int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **d_qn16, float **d_qne, cudaStream_t s);
+int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **d_qn16, float **d_qne, float **d_qde,
+                                cudaStream_t s);
 int tm_search_tc_prepared(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s);
 int tm_launch_temporal_smoothing(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal, int pal_size,
                                  const int32_t *d_frame_kf, int64_t nframes, int64_t npos, const int32_t *d_tile,
