@@ -345,6 +345,16 @@ def run_b200(args, rank, world, local_rank):
     ms = e0.elapsed_time(e1)
     st = tb.stats()
     tb.set_profiling(False)
+    # one more (untimed) pass with the tensor-core engine's error-model audit on: the largest observed coarse-score
+    # error over every re-ranked candidate, as a fraction of the bound the certificate assumes (must stay < 1)
+    audit = None
+    if local_rank == 0:
+        tb.reset_stats()
+        tb.set_profiling(2)
+        sft.search_local(d_rgb, out_idx=d_idx, out_err=d_err)
+        sa = tb.stats()
+        tb.set_profiling(False)
+        audit = {"max_observed_over_bound": float(sa["max_error_ratio"]), "candidates": int(sa["audited_candidates"])}
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -415,6 +425,7 @@ def run_b200(args, rank, world, local_rank):
             "phases_ms_per_step": {"descriptor": st["desc_ms"] / args.steps, "search": st["search_ms"] / args.steps,
                                    "coarse": st["coarse_ms"] / args.steps, "rerank": st["rerank_ms"] / args.steps},
             "fallback_queries_per_step": st["fallback_queries"] / args.steps,
+            "error_model_audit": audit,
             "gpu_launches": int(st["kernel_launches"]),
             "clocks": clk.summary(),
         }

@@ -223,8 +223,14 @@ typedef struct tm_stats {
     float coarse_ms;
     float rerank_ms;
     int64_t coarse_launches;
+    /* audit of the tensor-core engine's error model while profiling is on: the largest
+     * |coarse score + ||q16||^2 - exact distance| seen on a re-ranked candidate, divided by the bound the
+     * certificate assumes for it (2 e sqrt(d) + e^2 + a, csrc/search_tc.h).  Must stay below 1. */
+    float max_error_ratio;
+    int64_t audited_candidates;
 } tm_stats;
-/* tm_get_stats synchronises the library's stream when profiling is on. */
+/* tm_set_profiling: 0 off, 1 phase timing, 2 phase timing + error-model audit (slows the re-rank).
+ * tm_get_stats synchronises the library's stream when profiling is on. */
 TM_API int tm_set_profiling(int on);
 TM_API int tm_get_stats(tm_stats *out);
 TM_API int tm_reset_stats(void);

@@ -114,3 +114,51 @@ def test_tc_second_chance_for_rejected_queries(tb, oracle, layout):
         assert st["fallback_queries"] > 2000, st  # 40 rows of one cluster in one list: exact engine
     oi, od = oracle.knn_f32(ds, q[:64], 8)
     assert np.array_equal(te[:64].view(np.uint32), od.view(np.uint32))
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_tc_certificate_soundness_sweep(tb, seed):
+    """The certificate's error model (search_tc.h) against data it was not tuned on: offsets, heavy-tailed norms,
+    near-duplicate clusters at several jitter scales, integer rows.  Tensor-core results must equal the exact
+    engine's bit for bit whatever the coarse pass thinks."""
+    rng = np.random.default_rng(100 + seed)
+    n, nq = 6000, 1800
+    base = rng.standard_normal((n // 6, 192))
+    jitter = 10.0 ** rng.uniform(-5, -1, size=(6, 1, 1))
+    ds = (base[None] + jitter * rng.standard_normal((6, n // 6, 192))).reshape(n, 192)  # clusters, mixed scales
+    scale = np.where(rng.random((n, 1)) < 0.02, 40.0, 1.0)                              # a few huge rows
+    offset = rng.standard_normal((1, 192)) * 10.0 ** rng.uniform(-1, 2)                 # common offset
+    ds = (ds * scale + offset)
+    if seed == 5:
+        ds = np.round(ds * 4)  # integer rows (exactly representable after centring only by luck)
+    ds = ds.astype(np.float32)
+    pick = rng.integers(0, n, nq)
+    q = (ds[pick] + (10.0 ** rng.uniform(-4, 0, size=(nq, 1))) * rng.standard_normal((nq, 192))).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        for k in (1, 4, 8):
+            si, se, ti, te, st = _both(tb, t, q, k)
+            assert np.array_equal(se.view(np.uint32), te.view(np.uint32)), (seed, k)
+            assert np.array_equal(si, ti), (seed, k)
+
+
+def test_tc_error_model_audit(tb, oracle, small_case):
+    """Profiling level 2 reports the largest observed coarse-score error over all re-ranked candidates as a
+    fraction of the bound the certificate assumes (search_tc.h): it must be positive and well below 1."""
+    o = oracle
+    ds = o.psyv_tileset_f32(small_case["tiles"], small_case["pal"])
+    q = o.psyv_queries_f32(small_case["rgb"])
+    rng = np.random.default_rng(5)
+    cases = [(ds, q), (rng.standard_normal((4000, 192)).astype(np.float32) * 7 + 3,
+                       rng.standard_normal((1500, 192)).astype(np.float32) * 7 + 3)]
+    for rows, qq in cases:
+        with tb.KDTree.from_rows(rows) as t:
+            tb.set_engine(tb.ENGINE_TC)
+            tb.reset_stats()
+            tb.set_profiling(2)
+            for k in (1, 8):
+                t.search_batch(qq, k=k)
+            st = tb.stats()
+            tb.set_profiling(0)
+            tb.set_engine(tb.ENGINE_AUTO)
+        assert st["audited_candidates"] >= 2 * len(qq), st
+        assert 0.0 < st["max_error_ratio"] < 0.5, st

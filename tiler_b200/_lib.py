@@ -23,7 +23,7 @@ vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
 class TMStats(C.Structure):
     _fields_ = [("kernel_launches", i64), ("queries", i64), ("fallback_queries", i64),
                 ("desc_ms", f32), ("search_ms", f32), ("coarse_ms", f32), ("rerank_ms", f32),
-                ("coarse_launches", i64)]
+                ("coarse_launches", i64), ("max_error_ratio", f32), ("audited_candidates", i64)]
 
 
 # name -> (restype, argtypes); must list every TM_API symbol of include/tmann.h

@@ -47,7 +47,8 @@ def stats():
 
 
 def set_profiling(on):
-    check(lib.tm_set_profiling(int(bool(on))))
+    """False/0 off, True/1 phase timing, 2 phase timing + error-model audit of the tensor-core engine."""
+    check(lib.tm_set_profiling(int(on)))
 
 
 def reset_stats():

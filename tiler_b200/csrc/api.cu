@@ -23,11 +23,12 @@ bool g_inited = false;
 int g_device = -1, g_sms = 0;
 cudaStream_t g_stream = nullptr;
 std::mutex g_stats_mu;
-bool g_profiling = false;
+int g_profiling = 0; // 0 off, 1 phase timing, 2 phase timing + error-model audit
 struct ProfSpan { int tag; cudaEvent_t a, b; };
 std::vector<ProfSpan> g_spans;
 float g_ms[4] = {0, 0, 0, 0};
 int64_t g_coarse_launches = 0;
+unsigned long long *g_audit = nullptr; // device: [0] max error ratio (float bits), [1] audited candidates
 
 struct DevBuf { // simple RAII device allocation
     void *p = nullptr;
@@ -109,6 +110,15 @@ static void prof_collect() {
         cudaEventDestroy(sp.b);
     }
     g_spans.clear();
+}
+
+unsigned long long *tm_audit_slots() {
+    if (g_profiling < 2) return nullptr;
+    if (!g_audit) {
+        if (cudaMalloc(&g_audit, 16) != cudaSuccess) { g_audit = nullptr; return nullptr; }
+        cudaMemsetAsync(g_audit, 0, 16, g_stream);
+    }
+    return g_audit;
 }
 
 cudaStream_t tm_stream() { return g_stream; }
@@ -369,6 +379,17 @@ int tm_get_stats(tm_stats *out) {
     out->coarse_ms = g_ms[2];
     out->rerank_ms = g_ms[3];
     out->coarse_launches = g_coarse_launches;
+    out->max_error_ratio = 0.f;
+    out->audited_candidates = 0;
+    if (g_audit) {
+        unsigned long long a[2] = {0, 0};
+        cudaStreamSynchronize(g_stream);
+        if (cudaMemcpy(a, g_audit, 16, cudaMemcpyDeviceToHost) == cudaSuccess) {
+            const unsigned int bits = (unsigned int)a[0];
+            memcpy(&out->max_error_ratio, &bits, 4);
+            out->audited_candidates = (int64_t)a[1];
+        }
+    }
     return 0;
 }
 
@@ -378,11 +399,12 @@ int tm_reset_stats(void) {
     std::lock_guard<std::mutex> lk(g_stats_mu);
     for (float &m : g_ms) m = 0;
     g_coarse_launches = 0;
+    if (g_audit) cudaMemsetAsync(g_audit, 0, 16, g_stream);
     return 0;
 }
 
 int tm_set_profiling(int on) {
-    g_profiling = on != 0;
+    g_profiling = on < 0 ? 0 : on;
     return 0;
 }
 

@@ -52,7 +52,8 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     const float *__restrict__ cand_s, const int *__restrict__ cand_i, const float *__restrict__ cand_tau, int nlists, int kc,
     const float *__restrict__ qn16, const float *__restrict__ qne, const float *__restrict__ qde, float max_tnorm,
     float max_dnorm, int k, int maxv,
-    int *__restrict__ idx, float *__restrict__ err, int *__restrict__ fb_list, int *__restrict__ fb_count) {
+    int *__restrict__ idx, float *__restrict__ err, int *__restrict__ fb_list, int *__restrict__ fb_count,
+    unsigned long long *__restrict__ audit) {
     extern __shared__ uint8_t vlist_dyn[]; // [maxv][RR_THREADS] slot positions (< nlists * kc <= 256) of the live candidates
     uint8_t (*vlist)[RR_THREADS] = reinterpret_cast<uint8_t (*)[RR_THREADS]>(vlist_dyn);
     __shared__ __align__(16) float seg[STAGED ? RR_THREADS / 32 : 1][2][32 * RR_SEG_STRIDE];
@@ -128,6 +129,15 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
             d = act ? exact_dist(q + qc * dd, rows + (int64_t)ri * dd, dd) : 0.f;
         }
         if (!act) continue;
+        if (audit) { // error-model audit: observed |s~ + ||q16||^2 - d| against the bound the certificate assumes
+            const float sc = __ldg(cand_s + qg * C + vlist[v][threadIdx.x]);
+            const float nsumf = qne[qg] + max_tnorm;
+            const float e = tc_band_e(qde[qg], max_dnorm, nsumf), a = tc_band_a(nsumf);
+            const float ratio = fabsf(sc + qn16[qg] - d) / (2.f * e * sqrtf(d) + e * e + a);
+            if (ratio == ratio && __float_as_uint(ratio) > (unsigned int)audit[0])
+                atomicMax(audit, (unsigned long long)__float_as_uint(ratio));
+            atomicAdd(audit + 1, 1ull);
+        }
         // ascending by (distance, index)
         if (K1) {
             if (d < bd[0] || (d == bd[0] && ri < bi[0])) { bd[0] = d; bi[0] = ri; }
@@ -193,7 +203,7 @@ int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, 
         TM_CUDA(cudaFuncSetAttribute(rerank_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
         attr = true;
     }
-#define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, dyn, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, d_qdnorm, max_tnorm, max_dnorm, k, maxv, d_idx, d_err, d_fb_list, d_fb_count)
+#define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, dyn, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, d_qdnorm, max_tnorm, max_dnorm, k, maxv, d_idx, d_err, d_fb_list, d_fb_count, tm_audit_slots())
     if (k == 1) { if (staged) RR_LAUNCH(true, true); else RR_LAUNCH(true, false); }
     else { if (staged) RR_LAUNCH(false, true); else RR_LAUNCH(false, false); }
 #undef RR_LAUNCH

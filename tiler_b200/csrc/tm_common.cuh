@@ -61,6 +61,8 @@ static inline void tm_count_launch(int n = 1) { g_launches.fetch_add(n, std::mem
 
 int tm_ensure_device();
 int tm_prof_begin(int tag, cudaStream_t s); // returns a token (-1 when profiling is off)
+// error-model audit (profiling only): device slots {max ratio as float bits, candidate count}, or nullptr
+unsigned long long *tm_audit_slots();
 void tm_prof_end(int token, cudaStream_t s);
 cudaStream_t tm_stream();
 int tm_num_sms();
