@@ -1,16 +1,10 @@
 #!/bin/bash
-# Developer probe: time the coarse search kernel with its epilogue stages disabled (TM_TC_DBG):
-# 0 = full kernel, 1 = TMA + MMA pipeline only (no TMEM reads), 2 = + TMEM reads, no compare,
-# 3 = + group minima and votes, candidate slow path never taken.
-# Results are wrong in modes 1/2 by design; only coarse_ms is meaningful.
-for d in ${MODES:-0 1 2 3}; do
-  TM_TC_DBG=$d timeout 200 python bench.py --frames ${FRAMES:-37} --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > /tmp/dbg_$d.log 2>&1
-  python - "$d" <<'PY'
+# tuning sweep: where does the per-item overhead of the coarse pass come from (frame-sized batches)
+for dbg in 0 3 2 1; do for n in 1 8; do
+  echo "dbg=$dbg nsplit=$n"
+  TM_TC_DBG=$dbg TM_TC_NSPLIT=$n timeout 300 python scripts/frame_call_bench.py 2>&1 | python -c "
 import sys, json
-d = sys.argv[1]
-for l in open(f"/tmp/dbg_{d}.log"):
-    if l.startswith("{"):
-        j = json.loads(l)
-        print("dbg", d, j["phases_ms_per_step"], "TFLOP/s", j["roofline"]["achieved"], j["clocks"])
-PY
-done
+for l in sys.stdin:
+    if l.startswith('{'):
+        d = json.loads(l); print('  ', d['case'], 'coarse', round(d['device_ms_per_call']['coarse_ms'], 4))"
+done; done

@@ -324,13 +324,27 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     static const bool pair = !(getenv("TM_TC_PAIR") && atoi(getenv("TM_TC_PAIR")) == 0);
     const int tile_rows = pair ? T2_BN : TC_BN;
     const int total_tiles = (int)(h->n_pad / tile_rows);
-    // small query counts: split the row range so that every SM gets several work items
+    // Row split.  A work item costs its tiles plus a start-up (the candidate tracking of a fresh item hits on
+    // almost every group until its threshold has settled: measured 20-35 us = roughly 48 tile times), and the
+    // items are dealt round-robin to the resident CTA pairs, so the pass takes rounds x (tiles per item + 48).
+    // Few query blocks: split the rows so that every SM has work; many: one item per query block.
+    const int units = pair ? tm_num_sms() / 2 : tm_num_sms();
+    const int max_split = pair ? 8 : 16;
     int nsplit = 1;
-    const int want = pair ? 4 * tm_num_sms() : 8 * tm_num_sms();
-    if (qblocks < want) nsplit = (want + qblocks - 1) / qblocks;
-    if (finest_split) nsplit = pair ? 8 : 16;
+    {
+        double best = 1e30;
+        for (int ns = 1; ns <= max_split && ns <= (total_tiles + 3) / 4; ns++) {
+            const int per = (total_tiles + ns - 1) / ns;
+            const int items = qblocks * ((total_tiles + per - 1) / per);
+            const double cost = (double)((items + units - 1) / units) * (per + 48);
+            if (cost < best * 0.97) { best = cost; nsplit = ns; } // prefer fewer lists unless clearly better
+        }
+    }
+    if (finest_split) nsplit = max_split;
+    static const int nsplit_env = getenv("TM_TC_NSPLIT") ? atoi(getenv("TM_TC_NSPLIT")) : 0; // tuning knob
+    if (nsplit_env > 0 && !finest_split) nsplit = nsplit_env;
     if (nsplit > total_tiles / 4) nsplit = total_tiles / 4;
-    if (nsplit > (pair ? 8 : 16)) nsplit = pair ? 8 : 16;
+    if (nsplit > max_split) nsplit = max_split;
     if (nsplit < 1) nsplit = 1;
     int tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
     nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
