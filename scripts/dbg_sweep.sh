@@ -1,10 +1,8 @@
 #!/bin/bash
-# tuning sweep: where does the per-item overhead of the coarse pass come from (frame-sized batches)
-for dbg in 0 3 2 1; do for n in 1 8; do
-  echo "dbg=$dbg nsplit=$n"
-  TM_TC_DBG=$dbg TM_TC_NSPLIT=$n timeout 300 python scripts/frame_call_bench.py 2>&1 | python -c "
+# where the coarse pass spends its time at C2: TM_TC_DBG = 1 MMA only, 2 + TMEM reads, 3 + fast path, 0 everything
+for dbg in 1 2 3 0; do
+  echo -n "dbg=$dbg "
+  TM_TC_DBG=$dbg timeout 300 python bench.py --no-cpu-baseline --no-e2e --steps 4 2>&1 | tail -1 | python -c "
 import sys, json
-for l in sys.stdin:
-    if l.startswith('{'):
-        d = json.loads(l); print('  ', d['case'], 'coarse', round(d['device_ms_per_call']['coarse_ms'], 4))"
-done; done
+d = json.loads(sys.stdin.read()); print('coarse', round(d['phases_ms_per_step']['coarse'], 2), 'TF', round(d['roofline']['achieved'], 1), d['clocks']['sm_mhz'])"
+done
