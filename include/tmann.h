@@ -12,6 +12,14 @@
  * tm_last_error() gives the message.  Part 1 keeps the legacy shape (no error
  * channel: NULL handle / index -1 on failure).  There is no CPU fallback:
  * every call fails with TM_ENODEVICE when no sm_100 device is usable.
+ *
+ * Threads: every entry point may be called concurrently from any number of host
+ * threads over shared handles, as the encoder does (DoFrameTiling runs one frame
+ * per worker thread, main.pas:972).  Device work is serialised on one stream under
+ * a process-wide lock; frame-sized tm_frametiling_search calls copy pageable caller
+ * memory through per-thread pinned staging OUTSIDE that lock, so the host copies of
+ * one caller overlap the device work of another.  tm_last_error() is per thread.
+ * Destroying a handle while another thread still uses it is a caller error.
  */
 #ifndef TMANN_H
 #define TMANN_H
