@@ -216,6 +216,35 @@ def test_frametiling_fused(tb, oracle, small_case):
     assert np.median(err) < 0.1
 
 
+def test_frametiling_ragged_sizes_all_paths(tb, oracle, small_case):
+    """Every query count around the engine / padding / staging boundaries, through the host call (pageable
+    and pinned memory) and the device-pointer call, against the exact engine on the same descriptors."""
+    import torch
+    rgb = small_case["rgb"]
+    ds = oracle.psyv_tileset_f32(small_case["tiles"], small_case["pal"])
+    q = oracle.psyv_queries_f32(rgb)
+    oi, od = oracle.knn_f32(ds, q, 1)
+    with tb.KDTree.from_tileset(small_case["tiles"], small_case["pal"]) as t:
+        for n in (1, 2, 63, 64, 65, 127, 128, 255, 256, 257, 511, 513, 1000, 1499, 1500):
+            for off in (0, 3):
+                if off + n > len(rgb):
+                    continue
+                sl = slice(off, off + n)
+                gi, ge = t.frametiling_search(rgb[sl])                      # pageable host memory
+                assert np.array_equal(ge.view(np.uint32), od[sl, 0].view(np.uint32)), (n, off)
+                same = gi == oi[sl, 0]
+                assert np.all(same | (ge == 0) | np.isclose(ge, od[sl, 0])), (n, off)
+                pin = torch.from_numpy(np.ascontiguousarray(rgb[sl])).pin_memory()
+                pi, pe = t.frametiling_search(pin.numpy())                  # pinned host memory
+                assert np.array_equal(pi, gi) and np.array_equal(pe, ge), (n, off)
+                d = torch.from_numpy(np.ascontiguousarray(rgb[sl])).cuda()
+                di = torch.empty(n, dtype=torch.int32, device="cuda")
+                de = torch.empty(n, dtype=torch.float32, device="cuda")
+                t.frametiling_search(d, out_idx=di, out_err=de)             # device pointers
+                torch.cuda.synchronize()
+                assert np.array_equal(di.cpu().numpy(), gi) and np.array_equal(de.cpu().numpy(), ge), (n, off)
+
+
 def test_kmodes_assign_bit_exact(tb, oracle, small_case):
     o = oracle
     tiles, _ = o.gen_tileset(o.BASE_SEED + 9, 6000)
