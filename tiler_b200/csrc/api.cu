@@ -32,8 +32,8 @@ unsigned long long *g_audit = nullptr; // device: [0] max error ratio (float bit
 
 struct DevBuf { // simple RAII device allocation
     void *p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { return tm_check(cudaMalloc(&p, bytes ? bytes : 1), "cudaMalloc"); }
+    ~DevBuf() { if (p) tm_dev_free(p); }
+    int alloc(size_t bytes) { return tm_check(tm_dev_malloc(&p, bytes ? bytes : 1), "cudaMalloc"); }
     template <class T> T *as() { return static_cast<T *>(p); }
 };
 } // namespace
@@ -75,6 +75,13 @@ int tm_ensure_device() {
     if (cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking) != cudaSuccess) {
         tm_set_error("cudaStreamCreate failed");
         return TM_ENODEVICE;
+    }
+    {   // keep freed blocks in the driver's pool instead of returning them to the OS at every synchronisation
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            uint64_t keep = UINT64_MAX;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
     }
     g_device = dev;
     g_sms = prop.multiProcessorCount;
@@ -119,6 +126,11 @@ unsigned long long *tm_audit_slots() {
         cudaMemsetAsync(g_audit, 0, 16, g_stream);
     }
     return g_audit;
+}
+
+cudaError_t tm_dev_malloc_raw(void **p, size_t bytes) { return cudaMallocAsync(p, bytes ? bytes : 1, g_stream); }
+void tm_dev_free(void *p) {
+    if (p) cudaFreeAsync(p, g_stream);
 }
 
 cudaStream_t tm_stream() { return g_stream; }
@@ -193,9 +205,9 @@ static ANNkdtree *new_handle(int64_t n, int dd) {
 
 static void free_handle(ANNkdtree *h) {
     if (!h) return;
-    cudaFree(h->rows_f32); cudaFree(h->rows_f16); cudaFree(h->norms); cudaFree(h->norm_tiles); cudaFree(h->mean);
-    cudaFree(h->d_q1); cudaFree(h->d_i1); cudaFree(h->d_e1);
-    cudaFree(h->knn8_idx); cudaFree(h->knn8_err);
+    tm_dev_free(h->rows_f32); tm_dev_free(h->rows_f16); tm_dev_free(h->norms); tm_dev_free(h->norm_tiles); tm_dev_free(h->mean);
+    tm_dev_free(h->d_q1); tm_dev_free(h->d_i1); tm_dev_free(h->d_e1);
+    tm_dev_free(h->knn8_idx); tm_dev_free(h->knn8_err);
     free(h->h_tr_tile); free(h->h_tr_pal); free(h->h_tr_attrs);
     if (h->h_pin) cudaFreeHost(h->h_pin);
     free(h->tmap_rows);
@@ -207,9 +219,9 @@ static void free_handle(ANNkdtree *h) {
 // finish a handle whose rows_f32 is filled (on g_stream): build the tensor-core operand
 static ANNkdtree *finish_handle(ANNkdtree *h) {
     int r = 0;
-    if (!r) r = tm_check(cudaMalloc(&h->d_q1, sizeof(float) * h->dd), "cudaMalloc");
-    if (!r) r = tm_check(cudaMalloc(&h->d_i1, sizeof(int) * 16), "cudaMalloc");
-    if (!r) r = tm_check(cudaMalloc(&h->d_e1, sizeof(float) * 16), "cudaMalloc");
+    if (!r) r = tm_check(tm_dev_malloc(&h->d_q1, sizeof(float) * h->dd), "cudaMalloc");
+    if (!r) r = tm_check(tm_dev_malloc(&h->d_i1, sizeof(int) * 16), "cudaMalloc");
+    if (!r) r = tm_check(tm_dev_malloc(&h->d_e1, sizeof(float) * 16), "cudaMalloc");
     if (!r) r = tm_check(cudaMallocHost(&h->h_pin, sizeof(float) * (h->dd + 32)), "cudaMallocHost");
     if (!r) r = tm_prepare_dataset(h, g_stream);
     if (!r) r = sync_out();
@@ -224,7 +236,7 @@ ANNkdtree *tm_dataset_create(const float *rows, int64_t n, int dd, int is_device
     if (n > 0x7fffffff) { tm_set_error("tm_dataset_create: n too large"); return nullptr; }
     ANNkdtree *h = new_handle(n, dd);
     size_t bytes = sizeof(float) * (size_t)n * dd;
-    if (tm_check(cudaMalloc(&h->rows_f32, bytes ? bytes : 4), "cudaMalloc(rows)")) { free_handle(h); return nullptr; }
+    if (tm_check(tm_dev_malloc(&h->rows_f32, bytes ? bytes : 4), "tm_dev_malloc(rows)")) { free_handle(h); return nullptr; }
     if (is_device && sync_in()) { free_handle(h); return nullptr; }
     if (bytes && tm_check(cudaMemcpyAsync(h->rows_f32, rows, bytes, is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, g_stream), "copy rows")) {
         free_handle(h);

@@ -83,10 +83,10 @@ int tm_kf_compact(const uint8_t *d_used, int64_t n, int64_t **d_row_map_out, int
     int *pos = nullptr;
     void *tmp = nullptr;
     size_t tmp_bytes = 0;
-    TM_CUDA(cudaMalloc(&pos, sizeof(int) * (size_t)n));
+    TM_CUDA(tm_dev_malloc(&pos, sizeof(int) * (size_t)n));
     cub::TransformInputIterator<int, ByteToInt, const uint8_t *> in(d_used, ByteToInt());
     cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, in, pos, (int)n, s);
-    int r = tm_check(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1), "cudaMalloc(scan)");
+    int r = tm_check(tm_dev_malloc(&tmp, tmp_bytes ? tmp_bytes : 1), "tm_dev_malloc(scan)");
     if (!r) r = tm_check(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, in, pos, (int)n, s), "ExclusiveSum");
     tm_count_launch(2);
     int last_pos = 0;
@@ -96,16 +96,16 @@ int tm_kf_compact(const uint8_t *d_used, int64_t n, int64_t **d_row_map_out, int
     if (!r) r = tm_check(cudaStreamSynchronize(s), "sync(compact)");
     const int64_t cnt = (int64_t)last_pos + (last_flag ? 1 : 0);
     int64_t *row_map = nullptr;
-    if (!r) r = tm_check(cudaMalloc(&row_map, sizeof(int64_t) * (size_t)(cnt ? cnt : 1)), "cudaMalloc(row map)");
+    if (!r) r = tm_check(tm_dev_malloc(&row_map, sizeof(int64_t) * (size_t)(cnt ? cnt : 1)), "tm_dev_malloc(row map)");
     if (!r && cnt) {
         kf_scatter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d_used, pos, n, row_map);
         tm_count_launch();
         r = tm_check(cudaGetLastError(), "kf_scatter_kernel");
         if (!r) r = tm_check(cudaStreamSynchronize(s), "sync(scatter)"); // pos / tmp are freed below
     }
-    cudaFree(tmp);
-    cudaFree(pos);
-    if (r) { cudaFree(row_map); return r; }
+    tm_dev_free(tmp);
+    tm_dev_free(pos);
+    if (r) { tm_dev_free(row_map); return r; }
     *d_row_map_out = row_map;
     *h_count = cnt;
     return 0;

@@ -176,11 +176,11 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     double *part = nullptr;
     unsigned int *mx = nullptr;
     __half *r16 = nullptr;
-    TM_CUDA(cudaMalloc(&part, sizeof(double) * (size_t)nblocks * h->dd));
-    TM_CUDA(cudaMalloc(&mx, 4 * sizeof(unsigned int)));
-    TM_CUDA(cudaMalloc(&h->mean, sizeof(float) * h->dd));
-    TM_CUDA(cudaMalloc(&h->norms, sizeof(float) * n_pad));
-    TM_CUDA(cudaMalloc(&r16, sizeof(__half) * (size_t)n_pad * kp));
+    TM_CUDA(tm_dev_malloc(&part, sizeof(double) * (size_t)nblocks * h->dd));
+    TM_CUDA(tm_dev_malloc(&mx, 4 * sizeof(unsigned int)));
+    TM_CUDA(tm_dev_malloc(&h->mean, sizeof(float) * h->dd));
+    TM_CUDA(tm_dev_malloc(&h->norms, sizeof(float) * n_pad));
+    TM_CUDA(tm_dev_malloc(&r16, sizeof(__half) * (size_t)n_pad * kp));
     TM_CUDA(cudaMemsetAsync(mx, 0, 4 * sizeof(unsigned int), s));
     colsum_partial_kernel<<<nblocks, 192, 0, s>>>(h->rows_f32, h->n, h->dd, part);
     colmean_final_kernel<<<(h->dd + 63) / 64, 64, 0, s>>>(part, nblocks, h->n, h->dd, h->mean);
@@ -191,8 +191,8 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     unsigned int hmx[4];
     TM_CUDA(cudaMemcpyAsync(hmx, mx, sizeof hmx, cudaMemcpyDeviceToHost, s));
     TM_CUDA(cudaStreamSynchronize(s));
-    cudaFree(part);
-    cudaFree(mx);
+    tm_dev_free(part);
+    tm_dev_free(mx);
     float max_norm, max_abs;
     memcpy(&max_norm, &hmx[0], 4);
     memcpy(&max_abs, &hmx[1], 4);
@@ -202,10 +202,10 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     float S = 1.f;
     while (max_n16 / S > 32768.f && S < 32768.f) S *= 2.f;
     if (!(max_abs < 30000.f) || !(max_n16 / S < 60000.f)) { // outside the fp16 envelope (or NaN): exact engine only
-        cudaFree(r16);
+        tm_dev_free(r16);
         return 0;
     }
-    TM_CUDA(cudaMalloc(&h->norm_tiles, (size_t)(n_pad / 128) * 4096));
+    TM_CUDA(tm_dev_malloc(&h->norm_tiles, (size_t)(n_pad / 128) * 4096));
     normtile_kernel<<<(unsigned)((n_pad + 255) / 256), 256, 0, s>>>(h->norms, n_pad, 1.f / S, h->norm_tiles);
     tm_count_launch();
     TM_CUDA(cudaGetLastError());
@@ -424,11 +424,11 @@ static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int
     }
     int *list0 = nullptr, *ti = nullptr;
     float *qt = nullptr, *te = nullptr;
-    auto cleanup = [&]() { cudaFree(list0); cudaFree(ti); cudaFree(qt); cudaFree(te); };
-    r = tm_check(cudaMalloc(&list0, sizeof(int) * (size_t)nfb), "cudaMalloc(retry list)");
-    if (!r) r = tm_check(cudaMalloc(&qt, sizeof(float) * (size_t)nfb * h->dd), "cudaMalloc(retry queries)");
-    if (!r) r = tm_check(cudaMalloc(&ti, sizeof(int) * (size_t)nfb * k), "cudaMalloc(retry idx)");
-    if (!r) r = tm_check(cudaMalloc(&te, sizeof(float) * (size_t)nfb * k), "cudaMalloc(retry err)");
+    auto cleanup = [&]() { tm_dev_free(list0); tm_dev_free(ti); tm_dev_free(qt); tm_dev_free(te); };
+    r = tm_check(tm_dev_malloc(&list0, sizeof(int) * (size_t)nfb), "tm_dev_malloc(retry list)");
+    if (!r) r = tm_check(tm_dev_malloc(&qt, sizeof(float) * (size_t)nfb * h->dd), "tm_dev_malloc(retry queries)");
+    if (!r) r = tm_check(tm_dev_malloc(&ti, sizeof(int) * (size_t)nfb * k), "tm_dev_malloc(retry idx)");
+    if (!r) r = tm_check(tm_dev_malloc(&te, sizeof(float) * (size_t)nfb * k), "tm_dev_malloc(retry err)");
     if (r) { cleanup(); return r; }
     cudaMemcpyAsync(list0, g_tc.fb_list, sizeof(int) * (size_t)nfb, cudaMemcpyDeviceToDevice, s);
     {

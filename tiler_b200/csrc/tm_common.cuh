@@ -60,6 +60,14 @@ extern int g_engine;
 static inline void tm_count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 int tm_ensure_device();
+// Stream-ordered device memory from the driver's pool (cudaMallocAsync on the library stream, release threshold
+// unlimited): dataset buffers and per-call temporaries are recycled without cudaMalloc / cudaFree round trips
+// (cudaFree also synchronises the device).  Only for memory used on the library stream.
+cudaError_t tm_dev_malloc_raw(void **p, size_t bytes);
+template <class T> inline cudaError_t tm_dev_malloc(T **p, size_t bytes) {
+    return tm_dev_malloc_raw(reinterpret_cast<void **>(p), bytes);
+}
+void tm_dev_free(void *p);
 int tm_prof_begin(int tag, cudaStream_t s); // returns a token (-1 when profiling is off)
 // error-model audit (profiling only): device slots {max ratio as float bits, candidate count}, or nullptr
 unsigned long long *tm_audit_slots();
