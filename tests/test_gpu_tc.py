@@ -23,6 +23,18 @@ def _both(tb, tree, q, k):
     return si, se, ti, te, st
 
 
+def _both_auto(tb, tree, q, k=1):
+    tb.set_engine(tb.ENGINE_SIMT)
+    si, se = tree.search_batch(q, k=k)
+    tb.set_engine(tb.ENGINE_AUTO)
+    tb.reset_stats()
+    tb.set_profiling(True)
+    ti, te = tree.search_batch(q, k=k)
+    st = tb.stats()
+    tb.set_profiling(False)
+    return si, se, ti, te, st
+
+
 @pytest.mark.parametrize("ntiles,nq,k", [(512, 1500, 1), (2048, 5000, 1), (300, 257, 1), (700, 3000, 4), (512, 900, 8)])
 def test_tc_equals_simt_psyv(tb, oracle, ntiles, nq, k):
     o = oracle
@@ -162,3 +174,17 @@ def test_tc_error_model_audit(tb, oracle, small_case):
             tb.set_engine(tb.ENGINE_AUTO)
         assert st["audited_candidates"] >= 2 * len(qq), st
         assert 0.0 < st["max_error_ratio"] < 0.5, st
+
+
+def test_tc_nan_and_inf_rows_take_the_exact_engine(tb, oracle):
+    """A NaN or Inf anywhere in the dataset must be seen when the fp16 operand is built (the tensor-core path is
+    then not used for that dataset); results equal the exact engine's."""
+    rng = np.random.default_rng(21)
+    q = rng.standard_normal((300, 192)).astype(np.float32)
+    for bad in (np.nan, np.inf):
+        ds = rng.standard_normal((5000, 192)).astype(np.float32)
+        ds[4321, 17] = bad
+        with tb.KDTree.from_rows(ds) as t:
+            si, se, ti, te, st = _both_auto(tb, t, q)
+        assert np.array_equal(si, ti) and np.array_equal(se.view(np.uint32), te.view(np.uint32))
+        assert st["coarse_launches"] == 0

@@ -219,10 +219,6 @@ static void free_handle(ANNkdtree *h) {
 // finish a handle whose rows_f32 is filled (on g_stream): build the tensor-core operand
 static ANNkdtree *finish_handle(ANNkdtree *h) {
     int r = 0;
-    if (!r) r = tm_check(tm_dev_malloc(&h->d_q1, sizeof(float) * h->dd), "cudaMalloc");
-    if (!r) r = tm_check(tm_dev_malloc(&h->d_i1, sizeof(int) * 16), "cudaMalloc");
-    if (!r) r = tm_check(tm_dev_malloc(&h->d_e1, sizeof(float) * 16), "cudaMalloc");
-    if (!r) r = tm_check(cudaMallocHost(&h->h_pin, sizeof(float) * (h->dd + 32)), "cudaMallocHost");
     if (!r) r = tm_prepare_dataset(h, g_stream);
     if (!r) r = sync_out();
     if (r) { free_handle(h); return nullptr; }
@@ -333,6 +329,14 @@ static int search_one(ANNkdtree *akd, const float *q, int k, int *idxs, float *e
     if (valid(akd) || tm_ensure_device()) return -1;
     if (k < 1 || k > 16 || !q) return -1;
     std::lock_guard<std::mutex> lk(*akd->single_mu);
+    if (!akd->h_pin) { // scratch of the one-query entry points, on first use (pinned allocation is slow)
+        if (tm_dev_malloc(&akd->d_q1, sizeof(float) * akd->dd) || tm_dev_malloc(&akd->d_i1, sizeof(int) * 16) ||
+            tm_dev_malloc(&akd->d_e1, sizeof(float) * 16) ||
+            cudaMallocHost(&akd->h_pin, sizeof(float) * (akd->dd + 32)) != cudaSuccess) {
+            akd->h_pin = nullptr;
+            return -1;
+        }
+    }
     memcpy(akd->h_pin, q, sizeof(float) * akd->dd);
     if (cudaMemcpyAsync(akd->d_q1, akd->h_pin, sizeof(float) * akd->dd, cudaMemcpyHostToDevice, g_stream)) return -1;
     g_queries.fetch_add(1, std::memory_order_relaxed);

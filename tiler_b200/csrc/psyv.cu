@@ -28,7 +28,6 @@ struct PsyvConsts {
     double cu, cv, luma_div, luma_rcp, haar, rcp255;
 };
 
-__device__ double *g_dct_lut_dev = nullptr; // unused placeholder (lut passed by pointer)
 
 // One Haar level on the top-left N x N of an 8 x 8 (stride 8) block; same
 // operation order as WaveletGS: rows first into tx, then columns.
@@ -74,13 +73,6 @@ __device__ __forceinline__ double plane_value(int32_t col, int plane, const Psyv
     if (plane == 0) return y;
     if (plane == 1) return (T->f[b] - y) * K.cu;                         // main.pas:2675
     return (T->f[r] - y) * K.cv;                                         // main.pas:2676
-}
-
-__device__ __forceinline__ void store_row_f32(float *dst, const double (&a)[64]) {
-    float4 *d4 = reinterpret_cast<float4 *>(dst);
-#pragma unroll
-    for (int i = 0; i < 16; i++)
-        d4[i] = make_float4((float)a[4 * i], (float)a[4 * i + 1], (float)a[4 * i + 2], (float)a[4 * i + 3]);
 }
 
 // DCT-II branch main.pas:3075-3174: z = sum_{y,x} cpn*lut (sequential), optional Q weight, * cUVRatio
@@ -260,61 +252,83 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
     }
 }
 
-// tileset rows: thread = (row, plane); row r = ((p*ntiles + t)*2 + vmir)*2 + hmir
+// Palette colours -> (y, u, v) once per call: a palette has pal_size colours, a dataset renders each of them
+// thousands of times.  yuv is plane-major: [3][npal * pal_size].
+__global__ void psyv_palette_yuv_kernel(const int32_t *__restrict__ pals, int ncol, const PsyvTables *__restrict__ tabs,
+                                        PsyvConsts K, double *__restrict__ yuv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncol) return;
+    const int32_t col = pals[i];
+    yuv[i] = plane_value(col, 0, tabs, K);
+    yuv[ncol + i] = plane_value(col, 1, tabs, K);
+    yuv[2 * ncol + i] = plane_value(col, 2, tabs, K);
+}
+
+// tileset rows: thread = (row, plane); row r = ((p*ntiles + t)*2 + vmir)*2 + hmir.  The colour transform is a
+// gather from the (L1-resident) palette table; the float rows leave through padded shared memory so that the
+// block's 32 x 768 B go out as coalesced 16-byte stores.
 template <bool WAVELETS>
-__global__ void __launch_bounds__(192) psyv_tileset_kernel(const uint8_t *__restrict__ palpix, int64_t ntiles,
-                                                            const int32_t *__restrict__ pals, int npal,
+__global__ void __launch_bounds__(96) psyv_tileset_kernel(const uint8_t *__restrict__ palpix, int64_t ntiles,
+                                                            const double *__restrict__ yuv, int npal,
                                                             int pal_size, const uint8_t *__restrict__ tflags,
-                                                            const PsyvTables *__restrict__ tabs, PsyvConsts K,
+                                                            PsyvConsts K,
                                                             const double *__restrict__ lut,
                                                             const double *__restrict__ qw,
                                                             const int64_t *__restrict__ row_map, int64_t nrows,
                                                             float *__restrict__ out) {
-    __shared__ PsyvTables T;
-    for (int i = threadIdx.x; i < (int)(sizeof(PsyvTables) / 8); i += blockDim.x)
-        reinterpret_cast<double *>(&T)[i] = reinterpret_cast<const double *>(tabs)[i];
-    __syncthreads();
-    int plane = threadIdx.x / 64;
-    const int64_t orow = (int64_t)blockIdx.x * 64 + (threadIdx.x & 63); // output row
-    if (orow >= nrows) return;
-    // source (pal, tile, vmir, hmir): every combination in order, or the keyframe's used subset
-    const int64_t row = row_map ? row_map[orow] : orow;
-    int hmir = (int)(row & 1), vmir = (int)((row >> 1) & 1);
-    int64_t t = (row >> 2) % ntiles;
-    int p = (int)((row >> 2) / ntiles);
-    int fl = tflags ? tflags[t] : 0;
-    hmir ^= (fl & 1);          // hmir xor T^.HMirror main.pas:3912
-    vmir ^= ((fl >> 1) & 1);
-    const int32_t *pal = pals + (int64_t)p * pal_size;
-    // 64 palette indices as 4 x uint4
-    const uint4 *src = reinterpret_cast<const uint4 *>(palpix + t * 64);
-    uint32_t w[16];
+    __shared__ __align__(16) float sout[32 * PQ_OUT_STRIDE];
+    const int plane = threadIdx.x / 32, rl = threadIdx.x & 31;
+    const int64_t row0 = (int64_t)blockIdx.x * 32;
+    const int64_t orow = row0 + rl; // output row
+    const int nrow = (int)min((int64_t)32, nrows - row0);
+    if (rl < nrow) {
+        // source (pal, tile, vmir, hmir): every combination in order, or the keyframe's used subset
+        const int64_t row = row_map ? row_map[orow] : orow;
+        int hmir = (int)(row & 1), vmir = (int)((row >> 1) & 1);
+        const int64_t t = (row >> 2) % ntiles;
+        const int p = (int)((row >> 2) / ntiles);
+        const int fl = tflags ? tflags[t] : 0;
+        hmir ^= (fl & 1);          // hmir xor T^.HMirror main.pas:3912
+        vmir ^= ((fl >> 1) & 1);
+        const double *pal = yuv + (int64_t)plane * npal * pal_size + (int64_t)p * pal_size;
+        // 64 palette indices as 4 x uint4
+        const uint4 *src = reinterpret_cast<const uint4 *>(palpix + t * 64);
+        uint32_t w[16];
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-        uint4 v = __ldg(src + i);
-        w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
-    }
-    double a[64];
-#pragma unroll
-    for (int y = 0; y < 8; y++)
-#pragma unroll
-        for (int x = 0; x < 8; x++) {
-            // output pixel (x,y) takes source pixel (xx,yy) main.pas:3041-3046
-            int word_n = y * 2 + (x >> 2), word_v = (7 - y) * 2 + (x >> 2);
-            int word_hn = y * 2 + ((7 - x) >> 2), word_hv = (7 - y) * 2 + ((7 - x) >> 2);
-            uint32_t wn = vmir ? (hmir ? w[word_hv] : w[word_v]) : (hmir ? w[word_hn] : w[word_n]);
-            int sh = hmir ? ((7 - x) & 3) * 8 : (x & 3) * 8;
-            int pi = (wn >> sh) & 0xff;
-            a[y * 8 + x] = plane_value(__ldg(pal + pi), plane, &T, K);
+        for (int i = 0; i < 4; i++) {
+            uint4 v = __ldg(src + i);
+            w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
         }
-    float *dst = out + orow * TM_DCT + plane * 64;
-    if (WAVELETS) {
-        haar_level<8>(a, K.haar);
-        haar_level<4>(a, K.haar);
-        haar_level<2>(a, K.haar);
-        store_row_f32(dst, a);
-    } else {
-        dct_plane(a, lut, qw, plane, dst);
+        double a[64];
+#pragma unroll
+        for (int y = 0; y < 8; y++)
+#pragma unroll
+            for (int x = 0; x < 8; x++) {
+                // output pixel (x,y) takes source pixel (xx,yy) main.pas:3041-3046
+                int word_n = y * 2 + (x >> 2), word_v = (7 - y) * 2 + (x >> 2);
+                int word_hn = y * 2 + ((7 - x) >> 2), word_hv = (7 - y) * 2 + ((7 - x) >> 2);
+                uint32_t wn = vmir ? (hmir ? w[word_hv] : w[word_v]) : (hmir ? w[word_hn] : w[word_n]);
+                int sh = hmir ? ((7 - x) & 3) * 8 : (x & 3) * 8;
+                int pi = (wn >> sh) & 0xff;
+                a[y * 8 + x] = __ldg(pal + pi);
+            }
+        float *dst = sout + rl * PQ_OUT_STRIDE + plane * 64;
+        if (WAVELETS) {
+            haar_level<8>(a, K.haar);
+            haar_level<4>(a, K.haar);
+            haar_level<2>(a, K.haar);
+            store_row_smem(dst, a);
+        } else {
+            dct_plane(a, lut, qw, plane, dst);
+        }
+    }
+    __syncthreads();
+    {   // coalesced store of the block's rows (48 float4 per row)
+        float4 *dst = reinterpret_cast<float4 *>(out + row0 * TM_DCT);
+        for (int e = threadIdx.x; e < nrow * 48; e += 96) {
+            const int t = e / 48, j = e - t * 48;
+            dst[e] = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + j * 4);
+        }
     }
 }
 
@@ -601,14 +615,20 @@ int tm_launch_psyv_tileset_rows(const uint8_t *d_palpix, int64_t ntiles, const i
     int r = ensure_tables();
     if (r) return r;
     PsyvConsts K = make_consts();
-    unsigned grid = (unsigned)((nrows + 63) / 64);
+    unsigned grid = (unsigned)((nrows + 31) / 32);
     const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
+    const int ncol = npal * pal_size;
+    double *yuv = nullptr;
+    TM_CUDA(tm_dev_malloc(&yuv, sizeof(double) * 3 * (size_t)ncol));
+    psyv_palette_yuv_kernel<<<(unsigned)((ncol + 127) / 128), 128, 0, s>>>(d_pals, ncol, g_ps.tabs[gamma + 1], K, yuv);
     if (flags & TM_PSYV_WAVELETS)
-        psyv_tileset_kernel<true><<<grid, 192, 0, s>>>(d_palpix, ntiles, d_pals, npal, pal_size, d_tile_flags,
-                                                       g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_row_map, nrows, d_out);
+        psyv_tileset_kernel<true><<<grid, 96, 0, s>>>(d_palpix, ntiles, yuv, npal, pal_size, d_tile_flags, K, g_ps.lut, qw,
+                                                       d_row_map, nrows, d_out);
     else
-        psyv_tileset_kernel<false><<<grid, 192, 0, s>>>(d_palpix, ntiles, d_pals, npal, pal_size, d_tile_flags,
-                                                        g_ps.tabs[gamma + 1], K, g_ps.lut, qw, d_row_map, nrows, d_out);
+        psyv_tileset_kernel<false><<<grid, 96, 0, s>>>(d_palpix, ntiles, yuv, npal, pal_size, d_tile_flags, K, g_ps.lut, qw,
+                                                        d_row_map, nrows, d_out);
+    tm_dev_free(yuv); // stream-ordered: released after the kernel above
+    tm_count_launch();
     tm_count_launch();
     return tm_check(cudaGetLastError(), "psyv_tileset_kernel");
 }

@@ -25,6 +25,7 @@
 #include "search_tc.h"
 #include <cudaTypedefs.h>
 #include <math.h>
+#include <algorithm>
 
 namespace {
 
@@ -41,13 +42,20 @@ __global__ void colsum_partial_kernel(const float *__restrict__ rows, int64_t n,
     }
 }
 
+// one block per column: strided partial sums per thread, then a fixed-shape tree (deterministic)
 __global__ void colmean_final_kernel(const double *__restrict__ part, int nblocks, int64_t n, int dd,
                                      float *__restrict__ mean) {
-    int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= dd) return;
+    __shared__ double sh[128];
+    const int j = blockIdx.x;
     double acc = 0.0;
-    for (int b = 0; b < nblocks; b++) acc += part[(int64_t)b * dd + j]; // fixed order: deterministic
-    mean[j] = n > 0 ? (float)(acc / (double)n) : 0.f;
+    for (int b = threadIdx.x; b < nblocks; b += 128) acc += part[(int64_t)b * dd + j];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 64; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) mean[j] = n > 0 ? (float)(sh[0] / (double)n) : 0.f;
 }
 
 // one warp per row: centred fp16 operand (zero padded to kp), ||t~||^2 (fp32 of the rounded
@@ -58,39 +66,48 @@ __global__ void operand_kernel(const float *__restrict__ rows, int64_t n, int64_
                                float *__restrict__ dnorm, float pad_norm,
                                float out_scale, unsigned int *__restrict__ max_norm_bits,
                                unsigned int *__restrict__ max_abs_bits) {
-    int64_t r = (int64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x / 32);
-    int lane = threadIdx.x & 31;
-    if (r >= n_pad) return;
-    float s16 = 0.f, sex = 0.f, sde = 0.f, mabs = 0.f;
-    for (int j = lane; j < kp; j += 32) {
-        float v = 0.f;
-        if (r < n && j < dd) v = rows[r * dd + j] - mean[j];
-        __half h = __float2half_rn(v);
-        float hv = __half2float(h);
-        out16[r * kp + j] = __float2half_rn(out_scale * hv); // out_scale is a power of two: exact
-        s16 += hv * hv;
-        sex += v * v;
-        sde += (v - hv) * (v - hv); // v - hv is exact in fp32
-        mabs = fmaxf(mabs, fabsf(v));
-    }
+    const int lane = threadIdx.x & 31, wpb = blockDim.x / 32;
+    float wmax_norm = 0.f, wmax_abs = 0.f, wmax_n16 = 0.f, wmax_dn = 0.f; // this warp's maxima (dataset build only)
+    for (int64_t r = (int64_t)blockIdx.x * wpb + (threadIdx.x / 32); r < n_pad; r += (int64_t)gridDim.x * wpb) {
+        float s16 = 0.f, sex = 0.f, sde = 0.f, mabs = 0.f;
+        for (int j = lane; j < kp; j += 32) {
+            float v = 0.f;
+            if (r < n && j < dd) v = rows[r * dd + j] - mean[j];
+            __half h = __float2half_rn(v);
+            float hv = __half2float(h);
+            out16[r * kp + j] = __float2half_rn(out_scale * hv); // out_scale is a power of two: exact
+            s16 += hv * hv;
+            sex += v * v;
+            sde += (v - hv) * (v - hv); // v - hv is exact in fp32
+            mabs = fmaxf(mabs, fabsf(v));
+        }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        s16 += __shfl_xor_sync(0xffffffffu, s16, o);
-        sex += __shfl_xor_sync(0xffffffffu, sex, o);
-        sde += __shfl_xor_sync(0xffffffffu, sde, o);
-        mabs = fmaxf(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
+        for (int o = 16; o > 0; o >>= 1) {
+            s16 += __shfl_xor_sync(0xffffffffu, s16, o);
+            sex += __shfl_xor_sync(0xffffffffu, sex, o);
+            sde += __shfl_xor_sync(0xffffffffu, sde, o);
+            mabs = fmaxf(mabs, __shfl_xor_sync(0xffffffffu, mabs, o));
+        }
+        if (lane == 0) {
+            norm16[r] = (r < n) ? s16 : pad_norm;
+            if (norm_exact) norm_exact[r] = sqrtf(sex);
+            if (dnorm) dnorm[r] = sqrtf(sde);
+        }
+        if (r < n) { // NaN-propagating maxima: a NaN row must reach the host check (its bit pattern wins atomicMax)
+            const float en = sqrtf(sex), dn = sqrtf(sde);
+            wmax_norm = (en != en || en > wmax_norm) ? en : wmax_norm;
+            wmax_abs = (mabs != mabs || mabs > wmax_abs) ? mabs : wmax_abs;
+            wmax_n16 = (s16 != s16 || s16 > wmax_n16) ? s16 : wmax_n16;
+            wmax_dn = (dn != dn || dn > wmax_dn) ? dn : wmax_dn;
+        }
     }
+    // one set of atomics per warp (the per-row version serialised 10^5-10^6 atomics on three addresses)
     if (lane == 0) {
-        norm16[r] = (r < n) ? s16 : pad_norm;
-        if (norm_exact) norm_exact[r] = sqrtf(sex);
-        if (dnorm) dnorm[r] = sqrtf(sde);
-        if (r < n) {
-            if (max_norm_bits) atomicMax(max_norm_bits, __float_as_uint(sqrtf(sex)));
-            if (max_abs_bits) {
-                atomicMax(max_abs_bits, __float_as_uint(mabs));
-                atomicMax(max_abs_bits + 1, __float_as_uint(s16));
-                atomicMax(max_abs_bits + 2, __float_as_uint(sqrtf(sde)));
-            }
+        if (max_norm_bits) atomicMax(max_norm_bits, __float_as_uint(wmax_norm));
+        if (max_abs_bits) {
+            atomicMax(max_abs_bits, __float_as_uint(wmax_abs));
+            atomicMax(max_abs_bits + 1, __float_as_uint(wmax_n16));
+            atomicMax(max_abs_bits + 2, __float_as_uint(wmax_dn));
         }
     }
 }
@@ -183,8 +200,8 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     TM_CUDA(tm_dev_malloc(&r16, sizeof(__half) * (size_t)n_pad * kp));
     TM_CUDA(cudaMemsetAsync(mx, 0, 4 * sizeof(unsigned int), s));
     colsum_partial_kernel<<<nblocks, 192, 0, s>>>(h->rows_f32, h->n, h->dd, part);
-    colmean_final_kernel<<<(h->dd + 63) / 64, 64, 0, s>>>(part, nblocks, h->n, h->dd, h->mean);
-    operand_kernel<<<(unsigned)((n_pad + 7) / 8), 256, 0, s>>>(h->rows_f32, h->n, n_pad, h->dd, kp, h->mean, r16,
+    colmean_final_kernel<<<h->dd, 128, 0, s>>>(part, nblocks, h->n, h->dd, h->mean);
+    operand_kernel<<<(unsigned)std::min<int64_t>((n_pad + 7) / 8, 148 * 32), 256, 0, s>>>(h->rows_f32, h->n, n_pad, h->dd, kp, h->mean, r16,
                                                              h->norms, nullptr, nullptr, INFINITY, -2.f, mx, mx + 1);
     tm_count_launch(3);
     TM_CUDA(cudaGetLastError());
@@ -223,7 +240,7 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
 
 int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, int64_t nq_pad, __half *d_q16,
                             float *d_qnorm16, float *d_qnorm_exact, float *d_qdnorm, cudaStream_t s) {
-    operand_kernel<<<(unsigned)((nq_pad + 7) / 8), 256, 0, s>>>(d_q, nq, nq_pad, h->dd, h->kp, h->mean, d_q16,
+    operand_kernel<<<(unsigned)std::min<int64_t>((nq_pad + 7) / 8, 148 * 32), 256, 0, s>>>(d_q, nq, nq_pad, h->dd, h->kp, h->mean, d_q16,
                                                               d_qnorm16, d_qnorm_exact, d_qdnorm, 0.f, 1.f, nullptr, nullptr);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "operand_kernel(q)");
