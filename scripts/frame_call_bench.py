@@ -64,5 +64,29 @@ def main():
         tree.destroy()
 
 
+def kmodes_bin_case():
+    """KModesIter's unit of work (kmodes.pas:866-878): one bin of cBinSize = 960 points against all centroids,
+    host buffers, centroids re-uploaded every call because the Pascal side changes them between bins."""
+    import numpy as np
+    import tiler_b200 as tb
+    rng = np.random.default_rng(3)
+    X = rng.integers(0, 16, (960, 80), dtype=np.uint8)
+    X[:, 64:] = rng.integers(0, 2, (960, 16), dtype=np.uint8)
+    for k in (4096, 16384):
+        C = rng.integers(0, 16, (k, 80), dtype=np.uint8)
+        C[:, 64:] = rng.integers(0, 2, (k, 16), dtype=np.uint8)
+        for _ in range(3):
+            tb.kmodes_assign(X, C)
+        t0 = time.perf_counter()
+        for _ in range(50):
+            tb.kmodes_assign(X, C)
+        ms = (time.perf_counter() - t0) / 50 * 1e3
+        print(json.dumps({"case": "kmodes bin (960 points)", "centroids": k, "ms_per_call": ms,
+                          "pairs_per_s": 960 * k / ms * 1e3}))
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "kmodes":
+        kmodes_bin_case()
+        sys.exit(0)
     main()

@@ -286,6 +286,27 @@ def test_kmodes_assign_bit_exact(tb, oracle, small_case):
     assert np.all(clust == -1) and np.all(dis == np.uint64(2 ** 64 - 1))
 
 
+def test_kmodes_bin_sized_calls_split_centroids(tb, oracle):
+    """KModesIter works in bins of 960 points (kmodes.pas:847): few points, many centroids.  The launch splits
+    the centroid range over the grid; duplicates of a centroid in different ranges must still resolve to the
+    LAST index (kmodes.pas:414-415)."""
+    o = oracle
+    tiles, _ = o.gen_tileset(o.BASE_SEED + 77, 960 + 5000)
+    rows = o.kmodes_rows(tiles)
+    X, cent = rows[:960], rows[960:].copy()
+    cent[4900] = cent[10]     # same centroid far apart: the later one must win every tie
+    cent[2600] = cent[10]
+    cent[3000] = X[5]         # exact hits (dis 0) duplicated across ranges
+    cent[17] = X[5]
+    for sem in (tb.KM_ASM, tb.KM_GENERIC):
+        for n, k in ((960, 5000), (960, 513), (37, 5000), (1, 4097)):
+            clust, dis = tb.kmodes_assign(X[:n], cent[:k], sem)
+            wc, wd = o.kmodes_assign(X[:n], cent[:k], sem)
+            assert np.array_equal(clust, wc) and np.array_equal(dis, wd), (sem, n, k)
+    clust, _ = tb.kmodes_assign(X, cent)
+    assert clust[5] == 3000 and not np.any(clust == 10) and not np.any(clust == 2600)
+
+
 def test_kmodes_update_min_distance(tb, oracle):
     rng = np.random.default_rng(6)
     X = rng.integers(0, 16, (5000, 80)).astype(np.uint8)

@@ -13,6 +13,7 @@
 // Each thread owns one point (20 words in registers); centroids are staged in
 // shared memory in tiles and read as warp-wide broadcasts.
 #include "tm_common.cuh"
+#include <algorithm>
 
 namespace {
 
@@ -132,7 +133,12 @@ __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *_
                                                              const uint32_t *__restrict__ Cb,
                                                              const int *__restrict__ cent_wide,
                                                              int32_t *__restrict__ clust,
-                                                             uint64_t *__restrict__ dis) {
+                                                             uint64_t *__restrict__ dis, int64_t cchunk,
+                                                             int32_t *__restrict__ part_i,
+                                                             uint32_t *__restrict__ part_d) {
+    // blockIdx.y selects a range of cchunk centroids (few points: the centroids are split over the grid and
+    // merged by kmodes_merge_kernel; gridDim.y == 1: the whole set, results written directly)
+    const int64_t c_lo = (int64_t)blockIdx.y * cchunk, c_hi = min(k, c_lo + cchunk);
     __shared__ __align__(16) uint32_t cs[KM_TILE * KM_WORDS]; // byte rows, or bit-sliced rows (12 words each)
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t p[KM_WORDS];
@@ -156,8 +162,8 @@ __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *_
     if (fast) {
         uint32_t pb[KM_BWORDS];
         bitslice_row(p, pb);
-        for (int64_t c0 = 0; c0 < k; c0 += KM_TILE) {
-            int cnt = (int)min((int64_t)KM_TILE, k - c0);
+        for (int64_t c0 = c_lo; c0 < c_hi; c0 += KM_TILE) {
+            int cnt = (int)min((int64_t)KM_TILE, c_hi - c0);
             __syncthreads();
             const uint4 *src = reinterpret_cast<const uint4 *>(Cb + c0 * KM_BWORDS);
             for (int e = threadIdx.x; e < cnt * 3; e += blockDim.x) reinterpret_cast<uint4 *>(cs)[e] = __ldg(src + e);
@@ -184,8 +190,8 @@ __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *_
             }
         }
     } else {
-        for (int64_t c0 = 0; c0 < k; c0 += KM_TILE) {
-            int cnt = (int)min((int64_t)KM_TILE, k - c0);
+        for (int64_t c0 = c_lo; c0 < c_hi; c0 += KM_TILE) {
+            int cnt = (int)min((int64_t)KM_TILE, c_hi - c0);
             __syncthreads();
             const uint4 *src = reinterpret_cast<const uint4 *>(C + c0 * KM_WORDS);
             for (int e = threadIdx.x; e < cnt * 5; e += blockDim.x) reinterpret_cast<uint4 *>(cs)[e] = __ldg(src + e);
@@ -198,9 +204,30 @@ __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *_
         }
     }
     if (i < np) {
-        clust[i] = bi;
-        if (dis) dis[i] = (k > 0) ? (uint64_t)best : ~(uint64_t)0;
+        if (gridDim.y > 1) {
+            part_i[(int64_t)blockIdx.y * np + i] = bi;
+            part_d[(int64_t)blockIdx.y * np + i] = best;
+        } else {
+            clust[i] = bi;
+            if (dis) dis[i] = (k > 0) ? (uint64_t)best : ~(uint64_t)0;
+        }
     }
+}
+
+// centroid ranges in index order; "<=" keeps the later range on ties, i.e. the last index wins (kmodes.pas:414-415)
+__global__ void kmodes_merge_kernel(const int32_t *__restrict__ part_i, const uint32_t *__restrict__ part_d, int64_t np,
+                                    int nparts, int32_t *__restrict__ clust, uint64_t *__restrict__ dis) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= np) return;
+    uint32_t best = 0xffffffffu;
+    int bi = -1;
+    for (int p = 0; p < nparts; p++) {
+        const int ci = part_i[(int64_t)p * np + i];
+        const uint32_t d = part_d[(int64_t)p * np + i];
+        if (ci >= 0 && d <= best) { best = d; bi = ci; }
+    }
+    clust[i] = bi;
+    if (dis) dis[i] = (uint64_t)best;
 }
 
 template <int SEM>
@@ -359,6 +386,9 @@ struct KmScratch { // grow-only: bit-sliced centroids + wide flag
     uint32_t *cb = nullptr;
     int *flag = nullptr;
     size_t cap = 0;
+    int32_t *part_i = nullptr; // [parts][points] partial arg-min of the centroid-split launch
+    uint32_t *part_d = nullptr;
+    size_t cap_part = 0;
     std::mutex mu;
 } g_km;
 } // namespace
@@ -382,11 +412,37 @@ int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, 
         kmodes_pack_centroids_kernel<<<(unsigned)((k + 127) / 128), 128, 0, s>>>((const uint32_t *)d_c, k, g_km.cb, g_km.flag);
         tm_count_launch();
     }
-    unsigned grid = (unsigned)((np + 255) / 256);
+    const unsigned gx = (unsigned)((np + 255) / 256);
+    // Few points (KModesIter's bins of 960, kmodes.pas:847): thread-per-point alone would occupy a handful of SMs,
+    // so the centroids are split over gridDim.y in multiples of the shared-memory tile and merged afterwards.
+    int parts = 1;
+    const int64_t ctiles = (k + KM_TILE - 1) / KM_TILE;
+    if ((int64_t)gx < 2 * tm_num_sms() && ctiles > 1) {
+        parts = (int)std::min<int64_t>(ctiles, (4 * tm_num_sms() + gx - 1) / gx);
+        if (parts > 256) parts = 256;
+    }
+    const int64_t cchunk = parts > 1 ? ((ctiles + parts - 1) / parts) * KM_TILE : (k > 0 ? k : 1);
+    if (parts > 1) {
+        parts = (int)((k + cchunk - 1) / cchunk);
+        const size_t need = (size_t)parts * (size_t)np;
+        if (need > g_km.cap_part) {
+            cudaStreamSynchronize(s);
+            cudaFree(g_km.part_i); cudaFree(g_km.part_d);
+            g_km.part_i = nullptr; g_km.part_d = nullptr; g_km.cap_part = 0;
+            TM_CUDA(cudaMalloc(&g_km.part_i, sizeof(int32_t) * need));
+            TM_CUDA(cudaMalloc(&g_km.part_d, sizeof(uint32_t) * need));
+            g_km.cap_part = need;
+        }
+    }
+    const dim3 grid(gx, (unsigned)parts);
     if (sem == TM_KM_ASM)
-        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis);
+        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis, cchunk, g_km.part_i, g_km.part_d);
     else
-        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis);
+        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis, cchunk, g_km.part_i, g_km.part_d);
+    if (parts > 1) {
+        kmodes_merge_kernel<<<gx, 256, 0, s>>>(g_km.part_i, g_km.part_d, np, parts, d_clust, d_dis);
+        tm_count_launch();
+    }
     tm_count_launch();
     return tm_check(cudaGetLastError(), "kmodes_assign_kernel");
 }
