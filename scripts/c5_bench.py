@@ -16,7 +16,7 @@ def main():
     ap.add_argument("--tiles", type=int, default=262144)
     ap.add_argument("--queries", type=int, default=1 << 20)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--only", default="k8,k1,smooth")
+    ap.add_argument("--only", default="k8,k1,smooth,keyframe")
     args = ap.parse_args()
     import torch
     import tiler_b200 as tb
@@ -64,6 +64,32 @@ def main():
                               "fallback_queries": st.get("fallback_queries"),
                               "phases_ms": {"search": st["search_ms"], "coarse": st["coarse_ms"], "rerank": st["rerank_ms"]}}))
         tree.destroy()
+    if "keyframe" in only:
+        # PrepareGlobalFT + PrepareFrameTiling for one keyframe: 65 536 stored tiles, 16 palettes, the tilemaps of
+        # 30 frames at 1080p (972 000 items), ftMedium quality; host buffers, two keyframes (the second reuses the
+        # cached 8-NN of the stored tiles)
+        import time
+        import numpy as np
+        g = np.random.default_rng(11)
+        nt, npal = 65536, 16
+        t_h = tiles[:nt].cpu().numpy()
+        pals = g.integers(0, 1 << 24, (npal, 16), dtype=np.int64).astype(np.int32)
+        t0 = time.perf_counter()
+        gtree, _, _ = tb.KDTree.global_ft(t_h)
+        t_global = (time.perf_counter() - t0) * 1e3
+        cen = g.standard_normal((npal, 192))
+        res = []
+        for kf in range(2):
+            item_tile = g.integers(0, nt, 972000).astype(np.int32)
+            item_pal = g.integers(0, npal, 972000).astype(np.int32)
+            t0 = time.perf_counter()
+            st2 = gtree.keyframe_dataset(t_h, pals, item_pal, item_tile, quality=1, pal_tol=0.05, pal_centroids=cen)
+            res.append(((time.perf_counter() - t0) * 1e3, st2.n))
+            st2.destroy()
+        gtree.destroy()
+        print(json.dumps({"case": "keyframe preparation (host buffers)", "stored_tiles": nt, "palettes": npal,
+                          "items": 972000, "global_ft_ms": t_global, "first_keyframe_ms": res[0][0],
+                          "next_keyframe_ms": res[1][0], "stage2_rows": res[1][1]}))
     if "smooth" in only:
         # 1080p tilemap, 64 frames, 8 keyframes, 16 palettes: items persist with probability 0.7
         nframes, npos, nkf, npal = 64, 240 * 135, 8, 16
