@@ -81,6 +81,62 @@ def _worker(rank, world, port, ret):
         dist.destroy_process_group()
 
 
+def _kmodes_worker(rank, world, port, ret):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from oracle import tmoracle as o
+    from tiler_b200.shard import ShardedKModesAssign, point_shards
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        tiles, _ = o.gen_tileset(o.BASE_SEED + 31, 333 + 60)
+        rows = o.kmodes_rows(tiles)
+        X, cent = rows[:333], rows[333:].copy()       # 333 points over 2 ranks: ragged (167 + 166)
+        t_cent = torch.from_numpy(cent.copy())
+        if rank != 0:
+            t_cent.zero_()                            # the broadcast must overwrite it
+
+        def assign(xl, c):
+            cl, di = o.kmodes_assign(xl.numpy(), c.numpy())
+            return torch.from_numpy(cl.copy()), torch.from_numpy(di.astype(np.int64))
+
+        ska = ShardedKModesAssign(assign_fn=assign)
+        shards = point_shards(len(X), world)
+        a, b = shards[rank]
+        gc, gd = ska.assign(torch.from_numpy(X[a:b].copy()), t_cent, [q - p for p, q in shards])
+        assert np.array_equal(t_cent.numpy(), cent)
+        if rank == 0:
+            wc, wd = o.kmodes_assign(X, cent)
+            assert np.array_equal(gc.numpy(), wc) and np.array_equal(gd.numpy(), wd.astype(np.int64))
+        else:
+            assert gc is None and gd is None
+        ret[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+def _run_world2(target):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    ret = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=target, args=(r, 2, port, ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+    for p in procs:
+        if p.is_alive():
+            p.terminate()
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert dict(ret) == {0: "ok", 1: "ok"}
+
+
+def test_sharded_kmodes_assign_world2_gloo():
+    _run_world2(_kmodes_worker)
+
+
 def test_sharded_frametiling_world2_gloo():
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")

@@ -97,3 +97,53 @@ class ShardedFrameTiling:
         if self.tree is not None and hasattr(self.tree, "destroy"):
             self.tree.destroy()
         self.tree = None
+
+
+class ShardedKModesAssign:
+    """KModes assignment pass over several GPUs: points sharded, centroids replicated.
+
+    The reference thread-pools DoGMMD over points with shared, read-only centroids (kmodes.pas:825-835,
+    984-997).  One instance per rank: the centroids are broadcast from rank `src` (they change every iteration
+    on the Pascal side), each rank assigns its contiguous point range with the local library and (clust, dis)
+    are gathered to rank `dst`.  `assign_fn(X_local, centroids) -> (clust, dis)` defaults to the CUDA library;
+    the gloo tests inject the CPU oracle."""
+
+    def __init__(self, group=None, assign_fn=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self._assign = assign_fn or self._cuda_assign
+
+    @staticmethod
+    def _cuda_assign(X_local, centroids):
+        import torch
+        clust = torch.empty(X_local.shape[0], dtype=torch.int32, device=X_local.device)
+        dis = torch.empty(X_local.shape[0], dtype=torch.int64, device=X_local.device)
+        ann.kmodes_assign(X_local, centroids, ann.KM_ASM, out_clust=clust, out_dis=dis)
+        return clust, dis
+
+    def assign(self, X_local, centroids, sizes, src=0, dst=0):
+        """X_local: this rank's rows [n_r][80] (torch uint8); centroids: [k][80], preallocated on every rank;
+        sizes: points per rank (point_shards).  Returns (clust, dis) for all points on rank dst, else (None, None)."""
+        import torch
+        if self.world > 1:
+            self.dist.broadcast(centroids, src, group=self.group)
+        clust, dis = self._assign(X_local, centroids)
+        if self.world == 1:
+            return clust, dis
+        m = max(sizes)
+        pc = torch.full((m,), -1, dtype=clust.dtype, device=clust.device)
+        pd = torch.zeros(m, dtype=dis.dtype, device=dis.device)
+        pc[: clust.shape[0]] = clust
+        pd[: dis.shape[0]] = dis
+        gc = gd = None
+        if self.rank == dst:
+            gc = [torch.empty_like(pc) for _ in range(self.world)]
+            gd = [torch.empty_like(pd) for _ in range(self.world)]
+        self.dist.gather(pc, gc, dst, group=self.group)
+        self.dist.gather(pd, gd, dst, group=self.group)
+        if self.rank != dst:
+            return None, None
+        return (torch.cat([g[:n] for g, n in zip(gc, sizes)]), torch.cat([g[:n] for g, n in zip(gd, sizes)]))
