@@ -97,6 +97,8 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
         if (STAGED) {
             float acc = 0.f;
             float *sq = seg[warp][0], *sr = seg[warp][1];
+            // rounds after the first usually serve one or two lanes: stage only their rows
+            const unsigned actmask = __ballot_sync(0xffffffffu, act);
             for (int j0 = 0; j0 < dd; j0 += RR_SEG) {
                 const int seg4 = min(RR_SEG, dd - j0) >> 2; // float4 per row segment (dd % 4 == 0)
                 __syncwarp();
@@ -104,7 +106,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
                     const int rr = e >> 3, f = e & 7;
                     const int64_t qrow = __shfl_sync(0xffffffffu, qc, rr);
                     const int crow = __shfl_sync(0xffffffffu, ri, rr);
-                    if (f < seg4) {
+                    if (f < seg4 && ((actmask >> rr) & 1u)) {
                         *reinterpret_cast<float4 *>(sq + rr * RR_SEG_STRIDE + f * 4) =
                             __ldg(reinterpret_cast<const float4 *>(q + qrow * dd + j0) + f);
                         *reinterpret_cast<float4 *>(sr + rr * RR_SEG_STRIDE + f * 4) =
