@@ -102,3 +102,39 @@ def test_kmodes_c4_properties(env, oracle):
         assert o.dissim(cn[cs[j]], Xs[j], o.ASM) == ds_[j]
     wc, wd = o.kmodes_assign(Xs[:512], cn, o.ASM)  # full arg-min on a subsample against ALL centroids
     assert np.array_equal(wc, cs[:512]) and np.array_equal(wd.astype(np.int64), ds_[:512])
+
+
+@pytest.mark.parametrize("nq", [(1 << 16) - 1, 1 << 16, (1 << 16) + 77, 200_003])
+def test_coherence_order_is_invisible(env, oracle, nq):
+    """Batches of >= 65 536 queries are searched in a colour-sorted order inside the library (qorder.cu) and
+    scattered back: device-pointer and host-buffer calls must return, query for query, what the exact SIMT engine
+    returns in the caller's order (ragged sizes on both sides of the threshold), and the oracle's answer on a
+    subsample."""
+    torch, tb, dev, gen = env["torch"], env["tb"], env["dev"], env["gen"]
+    tiles, pal = env["synth_tileset"](torch, 2048, 16, gen)
+    rgb = env["synth_queries"](torch, nq, tiles, pal, gen)
+    with tb.KDTree.from_tileset(tiles, pal.view(1, -1)) as t:
+        i_tc = torch.empty(nq, dtype=torch.int32, device=dev)
+        e_tc = torch.empty(nq, dtype=torch.float32, device=dev)
+        tb.set_engine(tb.ENGINE_TC)
+        t.frametiling_search(rgb, out_idx=i_tc, out_err=e_tc)
+        h_i, h_e = t.frametiling_search(rgb.cpu().numpy())          # host buffers: 2^19-query chunks
+        tb.set_engine(tb.ENGINE_SIMT)
+        i_ex = torch.empty(nq, dtype=torch.int32, device=dev)
+        e_ex = torch.empty(nq, dtype=torch.float32, device=dev)
+        t.frametiling_search(rgb, out_idx=i_ex, out_err=e_ex)
+        tb.set_engine(tb.ENGINE_AUTO)
+        torch.cuda.synchronize()
+        assert torch.equal(i_tc, i_ex)
+        assert torch.equal(e_tc.view(torch.int32), e_ex.view(torch.int32))
+        assert np.array_equal(h_i, i_ex.cpu().numpy())
+        assert np.array_equal(h_e.view(np.uint32), e_ex.cpu().numpy().view(np.uint32))
+        # oracle on a strided subsample (positions spread over the whole batch)
+        sel = torch.arange(0, nq, max(1, nq // 256), device=dev)
+        ds = t.rows()
+        q = oracle.psyv_queries_f32(rgb[sel].cpu().numpy())
+        oi, od, nxt = oracle.knn_f64(ds, q, 1)
+        solid = (nxt - od[:, 0]) > 1e-5 * np.maximum(od[:, 0], 1e-12)
+        got_i, got_e = i_tc[sel].cpu().numpy(), e_tc[sel].cpu().numpy()
+        assert np.array_equal(got_i[solid], oi[solid, 0])
+        assert np.allclose(got_e, od[:, 0], rtol=1e-5, atol=1e-7)

@@ -115,6 +115,7 @@ struct PsyvOperandOut {
     float *qn16;       // sum of squares of the rounded values
     float *qne;        // Euclidean norm of the centred float row
     float *qde;        // Euclidean norm of the fp16 rounding error of the centred row
+    const int *perm;   // optional: output row p is computed from input tile perm[p] (coherence order, qorder.cu)
 };
 
 template <bool LINEAR>
@@ -155,10 +156,21 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
         const int32_t *src = rgb + q0 * 64;
         constexpr int PER_THREAD = (PQ_TILES * 64 + PQ_THREADS - 1) / PQ_THREADS;
         int32_t colv[PER_THREAD];
+        if (op.perm) { // gathered input: every tile is still one contiguous 256-byte read
+            __shared__ int64_t tile_src[PQ_TILES];
+            if ((int)threadIdx.x < ntile) tile_src[threadIdx.x] = (int64_t)__ldg(op.perm + q0 + threadIdx.x) * 64;
+            __syncthreads();
 #pragma unroll
-        for (int k = 0; k < PER_THREAD; k++) {
-            const int e = threadIdx.x + k * PQ_THREADS;
-            colv[k] = e < ntile * 64 ? __ldg(src + e) : 0;
+            for (int k = 0; k < PER_THREAD; k++) {
+                const int e = threadIdx.x + k * PQ_THREADS;
+                colv[k] = e < ntile * 64 ? __ldg(rgb + tile_src[e >> 6] + (e & 63)) : 0;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < PER_THREAD; k++) {
+                const int e = threadIdx.x + k * PQ_THREADS;
+                colv[k] = e < ntile * 64 ? __ldg(src + e) : 0;
+            }
         }
 #pragma unroll
         for (int k = 0; k < PER_THREAD; k++) {
@@ -570,12 +582,12 @@ PsyvConsts make_consts() {
 
 int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
                            cudaStream_t s) {
-    return tm_launch_psyv_queries_operand(d_rgb, nq, flags, gamma, d_out, nullptr, nullptr, nullptr, nullptr, nullptr, s);
+    return tm_launch_psyv_queries_operand(d_rgb, nq, flags, gamma, d_out, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, s);
 }
 
 int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
                                    const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, float *d_qde,
-                                   cudaStream_t s) {
+                                   const int *d_perm, cudaStream_t s) {
     if (gamma < -1 || gamma > 1) { tm_set_error("gamma must be -1, 0 or 1"); return TM_EINVAL; }
     if (nq == 0) return 0;
     int r = ensure_tables();
@@ -594,7 +606,7 @@ int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, 
     const bool linear = gamma < 0 && g_ps.linear_ok; // GammaCor = -1: c / 255.0 without the table
     const bool wav = (flags & TM_PSYV_WAVELETS) != 0;
     const PsyvTables *tabs = g_ps.tabs[gamma + 1];
-    const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne, d_qde};
+    const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne, d_qde, d_perm};
     if (wav && linear)
         psyv_queries_kernel<true, true><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     else if (wav)
