@@ -115,7 +115,7 @@ struct PsyvOperandOut {
     float *qn16;       // sum of squares of the rounded values
     float *qne;        // Euclidean norm of the centred float row
     float *qde;        // Euclidean norm of the fp16 rounding error of the centred row
-    const int *perm;   // optional: output row p is computed from input tile perm[p] (coherence order, qorder.cu)
+    const int *dst;    // optional: input tile i goes to output row dst[i] (coherence order, qorder.cu)
 };
 
 template <bool LINEAR>
@@ -145,6 +145,7 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
     double *cpn = reinterpret_cast<double *>(psm);
     double *ftab = reinterpret_cast<double *>(psm + PQ_CPN_BYTES);
     float *sout = reinterpret_cast<float *>(psm);
+    __shared__ int64_t dst_row[PQ_TILES]; // output row of each of the block's tiles
     const int64_t q0 = (int64_t)blockIdx.x * PQ_TILES;
     const int ntile = (int)min((int64_t)PQ_TILES, nq - q0);
     if (!LINEAR) {
@@ -156,22 +157,14 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
         const int32_t *src = rgb + q0 * 64;
         constexpr int PER_THREAD = (PQ_TILES * 64 + PQ_THREADS - 1) / PQ_THREADS;
         int32_t colv[PER_THREAD];
-        if (op.perm) { // gathered input: every tile is still one contiguous 256-byte read
-            __shared__ int64_t tile_src[PQ_TILES];
-            if ((int)threadIdx.x < ntile) tile_src[threadIdx.x] = (int64_t)__ldg(op.perm + q0 + threadIdx.x) * 64;
-            __syncthreads();
 #pragma unroll
-            for (int k = 0; k < PER_THREAD; k++) {
-                const int e = threadIdx.x + k * PQ_THREADS;
-                colv[k] = e < ntile * 64 ? __ldg(rgb + tile_src[e >> 6] + (e & 63)) : 0;
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < PER_THREAD; k++) {
-                const int e = threadIdx.x + k * PQ_THREADS;
-                colv[k] = e < ntile * 64 ? __ldg(src + e) : 0;
-            }
+        for (int k = 0; k < PER_THREAD; k++) {
+            const int e = threadIdx.x + k * PQ_THREADS;
+            colv[k] = e < ntile * 64 ? __ldg(src + e) : 0;
         }
+        // destination rows: requested together with the pixels (no dependent load), used only by the stores
+        if ((int)threadIdx.x < PQ_TILES)
+            dst_row[threadIdx.x] = (int)threadIdx.x < ntile ? (op.dst ? (int64_t)__ldg(op.dst + q0 + threadIdx.x) : q0 + threadIdx.x) : 0;
 #pragma unroll
         for (int k = 0; k < PER_THREAD; k++) {
             const int e = threadIdx.x + k * PQ_THREADS;
@@ -216,11 +209,10 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
         }
     }
     __syncthreads();
-    {   // coalesced store of the block's rows (48 float4 per row)
-        float4 *dst = reinterpret_cast<float4 *>(out + q0 * TM_DCT);
+    {   // coalesced store of the block's rows (48 float4 per row; rows are contiguous unless op.dst scatters them)
         for (int e = threadIdx.x; e < ntile * 48; e += PQ_THREADS) {
             const int t = e / 48, j = e - t * 48;
-            dst[e] = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + j * 4);
+            reinterpret_cast<float4 *>(out + dst_row[t] * TM_DCT)[j] = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + j * 4);
         }
     }
     if (op.q16) { // 16 lanes per row, 3 float4 each; six rows per pass (trip count uniform: shuffles need full warps)
@@ -231,7 +223,7 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
             const int t = grp + 6 * i;
             float s16 = 0.f, sex = 0.f, sde = 0.f;
             if (t < ntile) {
-                uint2 *drow = reinterpret_cast<uint2 *>(op.q16 + (q0 + t) * TM_DCT);
+                uint2 *drow = reinterpret_cast<uint2 *>(op.q16 + dst_row[t] * TM_DCT);
 #pragma unroll
                 for (int c = l16; c < 48; c += 16) {
                     const float4 x = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + c * 4);
@@ -256,9 +248,9 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
                 sde += __shfl_xor_sync(0xffffffffu, sde, o);
             }
             if (t < ntile && l16 == 0) {
-                op.qn16[q0 + t] = s16;
-                op.qne[q0 + t] = sqrtf(sex);
-                op.qde[q0 + t] = sqrtf(sde);
+                op.qn16[dst_row[t]] = s16;
+                op.qne[dst_row[t]] = sqrtf(sex);
+                op.qde[dst_row[t]] = sqrtf(sde);
             }
         }
     }
@@ -587,7 +579,7 @@ int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamm
 
 int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
                                    const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, float *d_qde,
-                                   const int *d_perm, cudaStream_t s) {
+                                   const int *d_dst, cudaStream_t s) {
     if (gamma < -1 || gamma > 1) { tm_set_error("gamma must be -1, 0 or 1"); return TM_EINVAL; }
     if (nq == 0) return 0;
     int r = ensure_tables();
@@ -606,7 +598,7 @@ int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, 
     const bool linear = gamma < 0 && g_ps.linear_ok; // GammaCor = -1: c / 255.0 without the table
     const bool wav = (flags & TM_PSYV_WAVELETS) != 0;
     const PsyvTables *tabs = g_ps.tabs[gamma + 1];
-    const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne, d_qde, d_perm};
+    const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne, d_qde, d_dst};
     if (wav && linear)
         psyv_queries_kernel<true, true><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     else if (wav)

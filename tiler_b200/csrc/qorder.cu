@@ -7,7 +7,8 @@
 // tile's mean colour (7 bits of Y, U, V each) takes the C2 coarse pass from 80-82 to 75.4 ms on the same box -
 // the same as sorting by the answer itself (scripts/query_order_experiment.py) - and makes the re-rank's row
 // gathers coherent as well.  The order is internal: descriptors are computed straight into sorted positions
-// (psyv_queries_kernel reads tile perm[p]) and the results are scattered back, so callers see their own order.
+// (psyv_queries_kernel reads the tiles in the caller's order - coalesced, no dependent load - and stores row i at
+// inv[i]) and the results are scattered back, so callers see their own order.
 // Any key gives correct results; the key only decides how fast.
 #include "tm_common.cuh"
 #include <cub/device/device_radix_sort.cuh>
@@ -60,6 +61,12 @@ __global__ void __launch_bounds__(256) query_key_kernel(const int32_t *__restric
     }
 }
 
+// inverse of the sorted order: query i goes to sorted position inv[perm[p]] = p
+__global__ void invert_order_kernel(const int *__restrict__ perm, int64_t n, int *__restrict__ inv) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) inv[perm[p]] = (int)p;
+}
+
 __global__ void scatter_query_results_kernel(const int *__restrict__ perm, int64_t n, const int *__restrict__ idx_s,
                                              const float *__restrict__ err_s, int *__restrict__ idx,
                                              float *__restrict__ err) {
@@ -79,9 +86,9 @@ size_t tm_query_order_temp_bytes(int64_t nq) {
     return bytes;
 }
 
-// d_perm[p] = index (within the batch) of the query that takes sorted position p
+// d_perm[p] = index (within the batch) of the query that takes sorted position p; d_inv = its inverse
 int tm_launch_query_order(const int32_t *d_rgb, int64_t nq, uint32_t *d_keys /* [2][nq] */, int *d_vals /* [nq] */,
-                          int *d_perm, void *d_tmp, size_t tmp_bytes, cudaStream_t s) {
+                          int *d_perm, int *d_inv, void *d_tmp, size_t tmp_bytes, cudaStream_t s) {
     if (nq == 0) return 0;
     if (nq > 0x7fffffff) { tm_set_error("query batch too large to order"); return TM_EINVAL; }
     const int64_t threads = nq * 16;
@@ -90,8 +97,9 @@ int tm_launch_query_order(const int32_t *d_rgb, int64_t nq, uint32_t *d_keys /* 
     static const int bits = getenv("TM_QORDER_BITS") ? atoi(getenv("TM_QORDER_BITS")) : QK_BITS; // tuning knob: top bits only
     const int lo = bits >= 1 && bits <= QK_BITS ? QK_BITS - bits : 0;
     TM_CUDA(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, d_keys, d_keys + nq, d_vals, d_perm, (int)nq, lo, QK_BITS, s));
-    tm_count_launch(); // the key kernel; CUB's sort kernels are library code and are not counted
-    return 0;
+    invert_order_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_perm, nq, d_inv);
+    tm_count_launch(2); // key + inversion kernels; CUB's sort kernels are library code and are not counted
+    return tm_check(cudaGetLastError(), "invert_order_kernel");
 }
 
 int tm_launch_scatter_query_results(const int *d_perm, int64_t nq, const int *d_idx_s, const float *d_err_s, int *d_idx,

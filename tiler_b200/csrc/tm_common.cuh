@@ -120,11 +120,11 @@ int tm_launch_kmodes_representatives(const uint8_t *d_X, int64_t np, const int32
 // query descriptors + (optionally) the tensor-core engine's query operand in one pass
 int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
                                    const float *d_mean, void *d_q16, float *d_qn16, float *d_qne, float *d_qde,
-                                   const int *d_perm, cudaStream_t s);
+                                   const int *d_dst, cudaStream_t s);
 // ---- coherence order of a query batch (qorder.cu): sort by a Morton code of the tile's mean colour
 size_t tm_query_order_temp_bytes(int64_t nq);
 int tm_launch_query_order(const int32_t *d_rgb, int64_t nq, uint32_t *d_keys /* [2][nq] */, int *d_vals /* [nq] */,
-                          int *d_perm, void *d_tmp, size_t tmp_bytes, cudaStream_t s);
+                          int *d_perm, int *d_inv, void *d_tmp, size_t tmp_bytes, cudaStream_t s);
 int tm_launch_scatter_query_results(const int *d_perm, int64_t nq, const int *d_idx_s, const float *d_err_s, int *d_idx,
                                     float *d_err, cudaStream_t s);
 // tensor-core engine with a query operand supplied by the caller: tm_tc_query_operand_buffers hands out the engine's
