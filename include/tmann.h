@@ -129,7 +129,11 @@ TM_API ANNkdtree *tm_tileset_dataset_create_dev(const uint8_t *d_palpix, int64_t
 TM_API int tm_dataset_read(const ANNkdtree *akd, float *h_rows);
 
 /* Fused FrameTiling hot loop (main.pas:4020-4038): RGB tiles -> descriptor ->
- * exact 1-NN in akd (dd must be 192).  out row index + squared-L2 err per query. */
+ * exact 1-NN in akd (dd must be 192).  out row index + squared-L2 err per query,
+ * in the caller's query order.  (Batches of >= 65 536 queries are searched in a
+ * colour-sorted order inside the library - similar tiles share the search kernel's
+ * warps, see qorder.cu - and scattered back; TM_QORDER=0 in the environment
+ * switches that off.  Results do not depend on it.) */
 TM_API int tm_frametiling_search(ANNkdtree *akd, const int32_t *h_rgb, int64_t nq, int flags,
                                  int gamma, int *h_idx, float *h_err);
 TM_API int tm_frametiling_search_dev(ANNkdtree *akd, const int32_t *d_rgb, int64_t nq, int flags,
