@@ -188,3 +188,24 @@ def test_tc_nan_and_inf_rows_take_the_exact_engine(tb, oracle):
             si, se, ti, te, st = _both_auto(tb, t, q)
         assert np.array_equal(si, ti) and np.array_equal(se.view(np.uint32), te.view(np.uint32))
         assert st["coarse_launches"] == 0
+
+
+@pytest.mark.parametrize("k", [2, 8])
+def test_tc_k_gt_1_seeded_items_equal_exact_engine(tb, oracle, k):
+    """k > 1 against 262 144 rows with enough query blocks for one work item per block (1 024 tiles per item): the
+    first 16 tiles of every item are scanned for the k smallest group minima only, seed the admission threshold and
+    are scanned again at the end (search_tc2_kernel.inc).  Results must still be the exact engine's, bit for bit;
+    clusters of near-identical rows inside the seed tiles make the seeded threshold tight from the start."""
+    rng = np.random.default_rng(29 + k)
+    n, nq = 262144, 20000
+    ds = rng.standard_normal((n, 192)).astype(np.float32)
+    ds[:4096:4] = ds[1:4096:4] + (1e-3 * rng.standard_normal((1024, 192))).astype(np.float32)  # near-duplicates up front
+    q = ds[rng.integers(0, n, nq)] + (0.05 * rng.standard_normal((nq, 192))).astype(np.float32)
+    q[:512] = ds[:2048:4][:512] + (1e-3 * rng.standard_normal((512, 192))).astype(np.float32)  # answers inside the seed tiles
+    with tb.KDTree.from_rows(ds) as t:
+        si, se, ti, te, st = _both(tb, t, q, k)
+    assert np.array_equal(se.view(np.uint32), te.view(np.uint32))
+    assert np.array_equal(si, ti)
+    assert st["fallback_queries"] < nq // 20, st
+    oi, od = oracle.knn_f32(ds, q[:32], k)
+    assert np.array_equal(te[:32].view(np.uint32), od.view(np.uint32))
