@@ -190,9 +190,11 @@ def test_tc_nan_and_inf_rows_take_the_exact_engine(tb, oracle):
         assert st["coarse_launches"] == 0
 
 
-@pytest.mark.parametrize("k", [2, 8])
-def test_tc_k_gt_1_seeded_items_equal_exact_engine(tb, oracle, k):
-    """k > 1 against 262 144 rows with enough query blocks for one work item per block (1 024 tiles per item): the
+@pytest.mark.parametrize("k", [1, 2, 8])
+def test_tc_long_items_equal_exact_engine(tb, oracle, k):
+    """k = 1: 1 024 tiles per work item select the norm-free kernel over the operand in scan order (rows sorted by
+    norm, candidate positions translated back through perm[]), here with the queries in the caller's order.
+    k > 1 against 262 144 rows with enough query blocks for one work item per block (1 024 tiles per item): the
     first 16 tiles of every item are scanned for the k smallest group minima only, seed the admission threshold and
     are scanned again at the end (search_tc2_kernel.inc).  Results must still be the exact engine's, bit for bit;
     clusters of near-identical rows inside the seed tiles make the seeded threshold tight from the start."""

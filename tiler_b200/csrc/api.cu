@@ -205,7 +205,7 @@ static ANNkdtree *new_handle(int64_t n, int dd) {
 
 static void free_handle(ANNkdtree *h) {
     if (!h) return;
-    tm_dev_free(h->rows_f32); tm_dev_free(h->rows_f16); tm_dev_free(h->norms); tm_dev_free(h->norm_tiles); tm_dev_free(h->mean);
+    tm_dev_free(h->rows_f32); tm_dev_free(h->rows_f16); tm_dev_free(h->norms); tm_dev_free(h->rows_f16s); tm_dev_free(h->norms_s); tm_dev_free(h->perm); tm_dev_free(h->norm_tiles); tm_dev_free(h->mean);
     tm_dev_free(h->d_q1); tm_dev_free(h->d_i1); tm_dev_free(h->d_e1);
     tm_dev_free(h->knn8_idx); tm_dev_free(h->knn8_err);
     free(h->h_tr_tile); free(h->h_tr_pal); free(h->h_tr_attrs);

@@ -13,6 +13,17 @@
 // eight epilogue warps read them back with tcgen05.ld (thread = query row) and keep each
 // query's KC smallest scores in registers.  The Q x N score matrix never reaches HBM.
 //
+// Scan order (k = 1).  The CTA-pair kernel's k = 1 variant does not spend an MMA on ||t~||^2 (1/13 of the tensor
+// time): its accumulator holds -2 q~.t~ only, and the epilogue's fast path tests
+//     min(acc over 32 columns) + (smallest norm of the warp's 128 columns) < tau,
+// a necessary condition that costs one add per tile; the exact norm is added only in the rare slow path.  For the
+// test to be tight the rows of a tile must have nearly equal norms, so k = 1 scans a second copy of the operand in
+// SCAN ORDER: rows sorted by ||t~||^2 (stable), cut into 256-row tiles, tiles dealt in a strided order so that
+// every stretch of the scan (and every row split) sees the whole norm range - in plain ascending order every
+// query's best score falls steadily along the scan and the slow path runs three times as often.  perm[] maps scan
+// position -> dataset row; the kernel translates when it writes its candidate lists.  k > 1 keeps the dataset
+// order and the norm MMA: near-identical rows (equal norms) would otherwise share one candidate list.
+//
 // Exactness.  s~ + ||q~||^2 is the exact squared distance between the ROUNDED vectors up to
 // fp32 summation error, so by the triangle inequality every row that is not a candidate
 // has true distance >= (sqrt(tau + ||q~||^2 - a) - e)^2 with tau the largest kept score,
@@ -24,6 +35,7 @@
 #include "ptx_sm100.cuh"
 #include "search_tc.h"
 #include <cudaTypedefs.h>
+#include <cub/device/device_radix_sort.cuh>
 #include <math.h>
 #include <algorithm>
 
@@ -137,6 +149,30 @@ __global__ void normtile_kernel(const float *__restrict__ norm16, int64_t n_pad,
     *reinterpret_cast<uint4 *>(t + 1024 + (rr / 8) * 64 + (rr % 8) * 8) = make_uint4(0, 0, 0, 0); // core 1
 }
 
+__global__ void iota_kernel(int *__restrict__ v, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) v[i] = (int)i;
+}
+
+// one thread per 16 bytes of the fp16 operand: rows, norms and the position -> row table in scan order.
+// Scan tile j holds the sorted 256-row block (j * stride) mod ntiles.
+__global__ void scan_order_kernel(const int *__restrict__ sorted_row, const float *__restrict__ norm_in,
+                                  const uint4 *__restrict__ in16, int64_t n, int64_t n_pad, int row_vec, int64_t stride,
+                                  uint4 *__restrict__ out16, float *__restrict__ norms, int *__restrict__ perm) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_pad * row_vec) return;
+    const int64_t pos = e / row_vec;
+    const int j = (int)(e - pos * row_vec);
+    const int64_t ntiles = n_pad >> 8, tile = pos >> 8;
+    const int64_t rank = (((tile * stride) % ntiles) << 8) + (pos & 255);
+    const int src = sorted_row[rank];
+    out16[e] = in16[(int64_t)src * row_vec + j];
+    if (j == 0) {
+        norms[pos] = norm_in[src];
+        perm[pos] = src < n ? src : -1;
+    }
+}
+
 PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
     static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
     if (fn) return fn;
@@ -232,9 +268,40 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     h->kp = kp;
     h->max_norm = max_norm;
     memcpy(&h->max_dnorm, &hmx[3], 4);
-    h->tmap_rows = malloc(2 * sizeof(CUtensorMap)); // [0] rows_f16, [1] norm tiles
+    {   // k = 1 scan order (header comment): stable sort by ||t~||^2 - non-negative floats order like their bit
+        // patterns, +inf padding last - then rows / norms / perm gathered tile by tile
+        uint32_t *k1 = nullptr;
+        int *v0 = nullptr, *v1 = nullptr;
+        void *tmp = nullptr;
+        size_t tmp_bytes = 0;
+        TM_CUDA(tm_dev_malloc(&k1, sizeof(uint32_t) * n_pad));
+        TM_CUDA(tm_dev_malloc(&v0, sizeof(int) * n_pad));
+        TM_CUDA(tm_dev_malloc(&v1, sizeof(int) * n_pad));
+        TM_CUDA(tm_dev_malloc(&h->norms_s, sizeof(float) * n_pad));
+        TM_CUDA(tm_dev_malloc(&h->perm, sizeof(int) * n_pad));
+        TM_CUDA(tm_dev_malloc(&h->rows_f16s, sizeof(__half) * (size_t)n_pad * kp));
+        const uint32_t *k0 = reinterpret_cast<const uint32_t *>(h->norms);
+        iota_kernel<<<(unsigned)((n_pad + 255) / 256), 256, 0, s>>>(v0, n_pad);
+        TM_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k0, k1, v0, v1, (int)n_pad, 0, 32, s));
+        TM_CUDA(tm_dev_malloc_raw(&tmp, tmp_bytes ? tmp_bytes : 4));
+        TM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k0, k1, v0, v1, (int)n_pad, 0, 32, s));
+        const int64_t ntiles = n_pad >> 8;
+        int64_t stride = (int64_t)((double)ntiles * 0.6180339887) | 1; // odd, near the golden section of the tile count
+        auto gcd = [](int64_t a, int64_t b) { while (b) { const int64_t t = a % b; a = b; b = t; } return a; };
+        while (gcd(stride, ntiles) != 1) stride += 2;
+        const int row_vec = kp / 8; // 16-byte pieces per operand row
+        const int64_t total = n_pad * row_vec;
+        scan_order_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(v1, h->norms, reinterpret_cast<const uint4 *>(r16), h->n, n_pad,
+                                                                          row_vec, stride, reinterpret_cast<uint4 *>(h->rows_f16s),
+                                                                          h->norms_s, h->perm);
+        tm_count_launch(2);
+        TM_CUDA(cudaGetLastError());
+        tm_dev_free(tmp); tm_dev_free(k1); tm_dev_free(v0); tm_dev_free(v1);
+    }
+    h->tmap_rows = malloc(3 * sizeof(CUtensorMap)); // [0] rows_f16, [1] norm tiles, [2] rows_f16s (k = 1 scan order)
     int r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows), r16, n_pad, kp);
     if (!r) r = make_tmap_norm(static_cast<CUtensorMap *>(h->tmap_rows) + 1, h->norm_tiles, n_pad / 128);
+    if (!r) r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows) + 2, h->rows_f16s, n_pad, kp);
     return r;
 }
 
@@ -254,6 +321,10 @@ int tm_make_query_tmap(void *tmap, const __half *d_q16, int64_t nq_pad, int kp) 
 #include "search_tc2_kernel.inc"
 
 // ------------------------------------------------------------------ host orchestration
+// set by the FrameTiling path around a search whose queries are in coherence order (qorder.cu); API lock held
+static bool g_tc_coherent = false;
+void tm_tc_set_coherent(bool on) { g_tc_coherent = on; }
+
 namespace {
 struct TcScratch {
     __half *q16 = nullptr;
@@ -375,10 +446,21 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     if ((r = make_tmap(&tq, g_tc.q16, nq_pad, h->kp))) return r;
     const CUtensorMap &tt = *static_cast<const CUtensorMap *>(h->tmap_rows);
     const CUtensorMap &tn = static_cast<const CUtensorMap *>(h->tmap_rows)[1];
+    const CUtensorMap &tts = static_cast<const CUtensorMap *>(h->tmap_rows)[2]; // k = 1: operand in scan order
     TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
+    // k = 1, long work items: norm-free accumulator over the operand in scan order (search_tc2_kernel.inc).  Its slow
+    // path costs more per call and an item starts on a tile of one norm level, so it needs long items, longer ones when
+    // the queries come in the caller's order (many slow-path calls).  Same-box A/B: sorted batch, 256 tiles per item
+    // 77.2 -> 75.2 ms (C2); 1 024 tiles +4 % (C3); unsorted frame calls: 256 tiles per item 0.301 -> 0.329 ms, 340-512
+    // tiles 2.24 -> 2.16 ms; 32-85 tiles per item -8 %.
+    static const int nf_env = getenv("TM_TC_NF_MIN") ? atoi(getenv("TM_TC_NF_MIN")) : 0; // tuning knob
+    const int nf_min = nf_env > 0 ? nf_env : (g_tc_coherent ? 192 : 320);
+    const bool normfree = k == 1 && pair && tiles_per_split >= nf_min && h->rows_f16s != nullptr;
     int tok = tm_prof_begin(2, s);
 #define TC_ARGS qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, g_tc.qde, h->max_norm, h->max_dnorm, k, s
-#define TC_LAUNCH(NCH, KC, K1) (pair ? launch_tc2<NCH, KC, K1>(tq, tt, tn, h->norm_scale, TC_ARGS) \
+#define TC_LAUNCH(NCH, KC, K1) (pair ? ((K1) && normfree ? launch_tc2<NCH, KC, K1, K1>(tq, tts, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS) \
+                                                    : launch_tc2<NCH, KC, K1, false>(tq, tt, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS)) \
+             \
                                      : launch_tc<NCH, KC, K1>(tq, tt, h->norm_tiles, h->norm_scale, TC_ARGS))
     if (k == 1) r = nch == 1 ? TC_LAUNCH(1, 8, true) : nch == 2 ? TC_LAUNCH(2, 8, true) : TC_LAUNCH(3, 8, true);
     else if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8, false) : nch == 2 ? TC_LAUNCH(2, 8, false) : TC_LAUNCH(3, 8, false);

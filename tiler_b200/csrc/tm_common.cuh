@@ -16,6 +16,9 @@
 //   rows_f16 [n_pad][kp]  fp16 operand of the tensor-core pass: mean-centred row, then the
 //                         fp32 ||t-mu||^2 split in three fp16 parts, zero padded to kp
 //   norms    [n]          float32 ||t-mu||^2 (fp32 from the unrounded centred row)
+//   rows_f16s [n_pad][kp] the same operand in the k = 1 kernel's SCAN ORDER (search_tc.cu: rows sorted by norm, cut
+//                         into 256-row tiles, tiles dealt in a strided order), norms_s [n_pad] their ||t~||^2
+//                         (+inf for padding rows), perm [n_pad] scan position -> dataset row (-1 for padding)
 //   mean     [dd]         float32 column mean (distance-invariant centring)
 struct ANNkdtree {
     uint32_t magic;
@@ -25,6 +28,9 @@ struct ANNkdtree {
     float *rows_f32;
     __half *rows_f16;
     float *norms;
+    __half *rows_f16s;
+    float *norms_s;
+    int *perm;
     __half *norm_tiles; // per 128-row tile: [||t~||^2 / S split in 3 fp16][zeros] as a no-swizzle UMMA operand image
     float norm_scale;   // S
     float *mean;
@@ -131,6 +137,7 @@ int tm_launch_scatter_query_results(const int *d_perm, int64_t nq, const int *d_
 // scratch (padding rows cleared) or returns 1 when the engine does not apply to this (dataset, k, nq)
 int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **d_qn16, float **d_qne, float **d_qde,
                                 cudaStream_t s);
+void tm_tc_set_coherent(bool on); // hint: the next searches' queries are in coherence order (qorder.cu)
 int tm_search_tc_prepared(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s);
 int tm_launch_temporal_smoothing(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal, int pal_size,
                                  const int32_t *d_frame_kf, int64_t nframes, int64_t npos, const int32_t *d_tile,
