@@ -1,6 +1,6 @@
 /* gen.c — deterministic synthetic inputs, built on the
  * reference's own LCG RandInt (kmodes.pas:82-86) so an FPC build could
- * regenerate identical data.  TEST INFRASTRUCTURE ONLY (see tmoracle.h).
+ * regenerate identical data.  TEST INFRASTRUCTURE ONLY, PARITY UNPINNED (see tmoracle.h).
  */
 #include "tmoracle.h"
 #include <string.h>
