@@ -1,16 +1,21 @@
 #!/usr/bin/env python
 """bench.py — FrameTiling best-tile search throughput on B200 (BASELINE.json metric).
 
-A step = one pass of the hot path (query PsyV descriptor -> exact 1-NN over the
-tileset in all 4 mirrors -> result) over the whole synthetic clip of the workload:
+A step = one pass of the hot path (query PsyV descriptor -> exact k-NN over the tileset in all 4 mirrors ->
+result) over the synthetic clip of the workload:
   N = 1 : configs[1]  720p x 300 frames, 8x8 tiles, 16k-tile set  (Q = 4 320 000, rows = 65 536)
-  N > 1 : the same clip PER GPU (weak scaling), tileset broadcast once over NCCL before
-          the timed region, per-step result gather to rank 0 inside it.
-`value`  : tile-queries/s, inputs resident in HBM, CUDA events on the launching stream.
-`e2e`    : same metric through the host-buffer C-ABI call (tm_frametiling_search):
-           pinned host RGB in, host idx/err out, copies inside the timed region.
-`--impl reference` : the reference's CPU loop (oracle port, all host threads) on a
-           bounded sample of the same workload.
+  N > 1 : configs[2]  1080p x 1000 frames, 64k-tile set (Q = 32 400 000, rows = 262 144), STRONG scaling: the clip is
+          cut into contiguous whole-frame shards, one per GPU; the tileset is broadcast once (NCCL) before the timed
+          region; every step ends with ONE all-gather of (idx, err) inside it.
+  --workload picks any other configuration (c1, c3 on one GPU, c5 = k = 8 on a 1 048 576-row set, c4 = KModes).
+`value`  : tile-queries/s, inputs resident in HBM, CUDA events on the launching stream, max over ranks.
+`e2e`    : same metric through the host-buffer C-ABI call: pinned host RGB in, host idx/err out, copies inside the
+           timed region.  For N > 1 it is ONE process (rank 0) driving all N GPUs through tm_set_devices +
+           tm_frametiling_search, which is how the single-process encoder would use the box; the process-per-GPU
+           figure is reported beside it (`e2e_process_per_gpu`).
+`--impl reference` : the reference's CPU loop (oracle port, all host threads) on a bounded sample of the workload.
+Synthetic inputs come from the reference's own LCG (RandInt, kmodes.pas:82-86), evaluated with torch
+on the device; tests/test_bench_synth.py checks them against oracle/gen.c.
 """
 import argparse
 import json
@@ -26,13 +31,22 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    # name: (frames, tilemap positions per frame, tiles)
-    "c1_320x240_64f_4k": (64, 40 * 30, 4096),
-    "c2_720p_300f_16k": (300, 160 * 90, 16384),
-    "c3_1080p_1000f_64k": (1000, 240 * 135, 65536),
+    # name: frames, tilemap positions per frame, tiles (x 4 mirrors = dataset rows), k, BASELINE.json config index
+    "c1_320x240_64f_4k": dict(frames=64, pos=40 * 30, tiles=4096, k=1, cfg=0),
+    "c2_720p_300f_16k": dict(frames=300, pos=160 * 90, tiles=16384, k=1, cfg=1),
+    "c3_1080p_1000f_64k": dict(frames=1000, pos=240 * 135, tiles=65536, k=1, cfg=2),
+    # C5: the UseOne shape (k = 8 neighbours + FP32 re-rank, main.pas:3804, 3830) on the PsyV descriptors of a 4K clip.
+    # The full clip is 259.2 M queries x 1 048 576 rows = 1.04e17 flop per step (12 s on 8 B200): the bench times a
+    # stated 64-frame subsample of it (strong-scaled over the GPUs), flagged in config.sample.
+    "c5_4k_2000f_256k_k8": dict(frames=2000, pos=480 * 270, tiles=262144, k=8, cfg=4, sample_frames=64),
+    # C4: GlobalTiling KModes assignment pass, 1 048 576 points -> 16 384 centroids (kmodes.pas:984-997)
+    "c4_kmodes_1m_16k": dict(points=1 << 20, centroids=1 << 14, cfg=3),
 }
 D = 192
 METRIC = "FrameTiling tile-queries/sec"
+BASE_SEED = 0x42381337  # kmodes.pas:930
+GOLD = 0x9E3779B9
+M32 = 0xFFFFFFFF
 
 
 def parse():
@@ -41,55 +55,131 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c2_720p_300f_16k", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="default: c2 on one GPU, c3 (strong-scaled) on several")
     ap.add_argument("--engine", default="auto", choices=["auto", "simt", "tc"])
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU-baseline sample time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--kernels", action="store_true",
-                    help="also time the HBM-bound helper kernels and the KModes assignment pass (C4) and add them as `kernels`")
+    ap.add_argument("--no-kernels", action="store_true", help="skip the secondary-kernel block (`kernels`)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the unplanted-query pass and the call-pattern block")
     ap.add_argument("--frames", type=int, default=0, help="override the clip length (profiling runs only)")
     return ap.parse_args()
 
 
-# ------------------------------------------------------------------ synthetic data (torch, on device)
-def synth_tileset(torch, ntiles, pal_size, gen):
-    """random base + linear gradient + +-1 noise per tile, like SURVEY.md §8d; palette sorted by luma"""
-    dev = gen.device
-    pal = torch.randint(0, 256, (pal_size, 3), generator=gen, device=dev)
-    luma = 2126 * pal[:, 0] + 7152 * pal[:, 1] + 722 * pal[:, 2]
-    pal = pal[torch.argsort(luma)]
-    pal_i32 = (pal[:, 0] | (pal[:, 1] << 8) | (pal[:, 2] << 16)).to(torch.int32)  # $00BBGGRR
-    base = torch.randint(0, pal_size, (ntiles, 1, 1), generator=gen, device=dev)
-    gx = torch.randint(-3, 4, (ntiles, 1, 1), generator=gen, device=dev)
-    gy = torch.randint(-3, 4, (ntiles, 1, 1), generator=gen, device=dev)
-    div = torch.randint(2, 8, (ntiles, 1, 1), generator=gen, device=dev)
-    xs = torch.arange(8, device=dev).view(1, 1, 8) - 4
-    ys = torch.arange(8, device=dev).view(1, 8, 1) - 4
-    noise = torch.randint(-1, 2, (ntiles, 8, 8), generator=gen, device=dev)
-    t = base + torch.div(gx * xs + gy * ys, div, rounding_mode="trunc") + noise
-    return t.clamp_(0, pal_size - 1).to(torch.uint8).reshape(ntiles, 64).contiguous(), pal_i32.contiguous()
+def pick_workload(args, world):
+    return args.workload or ("c2_720p_300f_16k" if world == 1 else "c3_1080p_1000f_64k")
 
 
-def synth_queries(torch, nq, tiles, pal_i32, gen, noise=6, chunk=1 << 20):
-    """planted (tile, mirror) rendered through the palette + uniform noise; 1/16 pure random RGB"""
-    dev = gen.device
-    out = torch.empty((nq, 64), dtype=torch.int32, device=dev)
-    t3 = tiles.view(-1, 8, 8).long()
-    pal = torch.stack([pal_i32 & 0xff, (pal_i32 >> 8) & 0xff, (pal_i32 >> 16) & 0xff], -1).long()
-    for q0 in range(0, nq, chunk):
-        c = min(chunk, nq - q0)
-        tid = torch.randint(0, tiles.shape[0], (c,), generator=gen, device=dev)
-        hm = torch.randint(0, 2, (c, 1, 1), generator=gen, device=dev).bool()
-        vm = torch.randint(0, 2, (c, 1, 1), generator=gen, device=dev).bool()
+# ------------------------------------------------------------------ synthetic data: the reference's LCG, vectorised
+# RandInt (kmodes.pas:82-86): Seed := Seed * $08088405 + 1; Result := (Seed * Range) shr 32.  oracle/gen.c seeds
+# every tile / query separately (s0 + index * golden), so the streams are independent and one torch op advances all
+# of them: the generators below are gen.c restated on int64 tensors, draw for draw.
+class _Lcg:
+    def __init__(self, torch, seeds):
+        self.torch, self.s = torch, seeds
+
+    def draw(self, rng):
+        self.s = (self.s * 0x08088405 + 1) & M32
+        return (self.s * rng) >> 32
+
+
+def lcg_scalar(seed, rng):
+    seed = (seed * 0x08088405 + 1) & M32
+    return seed, (seed * rng) >> 32
+
+
+def lcg_palette(seed, pal_size=16):
+    """tmo_gen_palette: pal_size x (r, g, b) draws, stable insertion sort by integer luma.  Returns (list, seed)."""
+    cols = []
+    for _ in range(pal_size):
+        seed, r = lcg_scalar(seed, 256)
+        seed, g = lcg_scalar(seed, 256)
+        seed, b = lcg_scalar(seed, 256)
+        cols.append((b << 16) | (g << 8) | r)
+    luma = lambda c: 2126 * (c & 0xff) + 7152 * ((c >> 8) & 0xff) + 722 * ((c >> 16) & 0xff)
+    cols.sort(key=luma)  # Python's sort is stable, like the insertion sort with a strict comparison
+    return cols, seed
+
+
+def lcg_tileset(torch, seed, ntiles, pal_size, dev):
+    """tmo_gen_tileset + PrepareTileMirrors (main.pas:4049-4069).  Returns (uint8 [ntiles][64], next seed)."""
+    t = torch.arange(ntiles, dtype=torch.int64, device=dev)
+    g = _Lcg(torch, (seed + t * GOLD) & M32)
+    g.draw(2)
+    base = g.draw(pal_size)
+    gx, gy = g.draw(7) - 3, g.draw(7) - 3
+    div = 2 + g.draw(6)
+    px = torch.empty((ntiles, 8, 8), dtype=torch.int64, device=dev)
+    for y in range(8):
+        for x in range(8):
+            num = gx * (x - 4) + gy * (y - 4)
+            q = torch.div(num, div, rounding_mode="trunc")  # C integer division
+            px[:, y, x] = (base + q + g.draw(3) - 1).clamp_(0, pal_size - 1)
+    # brightest quadrant to the top left, first wins ties, order (vf, hf) = (0,0), (0,1), (1,0), (1,1)
+    sums = torch.stack([px[:, 0:4, 0:4].sum((1, 2)), px[:, 0:4, 4:8].sum((1, 2)),
+                        px[:, 4:8, 0:4].sum((1, 2)), px[:, 4:8, 4:8].sum((1, 2))], 1)
+    ties = sums == sums.max(1, keepdim=True).values
+    order = torch.arange(4, device=dev).view(1, 4).expand_as(sums)
+    best = torch.where(ties, order, torch.full_like(order, 4)).min(1).values  # first maximum wins, like `v > bestV`
+    hf, vf = (best & 1).bool(), (best >> 1).bool()
+    px = torch.where(hf.view(-1, 1, 1), px.flip(2), px)
+    px = torch.where(vf.view(-1, 1, 1), px.flip(1), px)
+    return px.reshape(ntiles, 64).to(torch.uint8).contiguous(), (seed + ntiles * GOLD + 1) & M32
+
+
+def lcg_queries(torch, seed, q_begin, q_end, tiles, pal, dev, noise=6, unplanted_from=None, chunk=1 << 21):
+    """tmo_gen_queries for the global query range [q_begin, q_end): planted (tile, mirror) rendered through the
+    palette + uniform noise; 1 in 16 pure random RGB.  int32 [n][64] $00BBGGRR."""
+    src = tiles if unplanted_from is None else unplanted_from
+    ntiles = src.shape[0]
+    t3 = src.view(-1, 8, 8).long()
+    palt = torch.tensor(pal, dtype=torch.int64, device=dev)
+    out = torch.empty((q_end - q_begin, 64), dtype=torch.int32, device=dev)
+    for c0 in range(q_begin, q_end, chunk):
+        c1 = min(q_end, c0 + chunk)
+        qi = torch.arange(c0, c1, dtype=torch.int64, device=dev)
+        g = _Lcg(torch, (seed + qi * GOLD) & M32)
+        g.draw(2)
+        rnd = g.draw(16) == 0
+        s_branch = g.s.clone()
+        # pure random branch: 64 draws of 2^24
+        rnd_px = torch.empty((c1 - c0, 64), dtype=torch.int64, device=dev)
+        for i in range(64):
+            rnd_px[:, i] = g.draw(1 << 24)
+        # planted branch
+        g.s = s_branch
+        tid = g.draw(ntiles)
+        hm, vm = g.draw(2).bool(), g.draw(2).bool()
         px = t3[tid]
-        px = torch.where(hm, px.flip(2), px)
-        px = torch.where(vm, px.flip(1), px)
-        rgb = pal[px.reshape(c, 64)] + torch.randint(-noise, noise + 1, (c, 64, 3), generator=gen, device=dev)
-        rnd = torch.randint(0, 16, (c, 1, 1), generator=gen, device=dev) == 0
-        rgb = torch.where(rnd, torch.randint(0, 256, (c, 64, 3), generator=gen, device=dev), rgb).clamp_(0, 255)
-        out[q0:q0 + c] = (rgb[..., 0] | (rgb[..., 1] << 8) | (rgb[..., 2] << 16)).to(torch.int32)
-    return out
+        px = torch.where(hm.view(-1, 1, 1), px.flip(2), px)
+        px = torch.where(vm.view(-1, 1, 1), px.flip(1), px)
+        col = palt[px.reshape(-1, 64)]
+        pl = torch.empty((c1 - c0, 64), dtype=torch.int64, device=dev)
+        for i in range(64):
+            ch = []
+            for k in range(3):
+                v = ((col[:, i] >> (8 * k)) & 0xff) + g.draw(2 * noise + 1) - noise
+                ch.append(v.clamp_(0, 255))
+            pl[:, i] = (ch[2] << 16) | (ch[1] << 8) | ch[0]
+        out[c0 - q_begin:c1 - q_begin] = torch.where(rnd.view(-1, 1), rnd_px, pl).to(torch.int32)
+    return out, (seed + 0 * GOLD) & M32
+
+
+def synth_case(torch, wl, dev, with_tiles=True):
+    """palette, tileset and the query seed of a workload (BASE_SEED + BASELINE config index)"""
+    seed = (BASE_SEED + wl["cfg"]) & M32
+    pal, seed = lcg_palette(seed, 16)
+    tiles, seed = lcg_tileset(torch, seed, wl["tiles"], 16, dev)
+    return pal, tiles, seed
+
+
+def kmodes_rows_torch(torch, tiles, pal_size=16):
+    """WriteTileDatasetLine main.pas:4167-4183 + GetTilePalZoneThres 4142-4165: 64 palette indices + 16 zone flags"""
+    zone = (tiles.long() * 16) // pal_size
+    thres = pal_size // 16
+    flags = torch.stack([(zone == z).sum(1) > thres for z in range(16)], 1).to(torch.uint8)
+    return torch.cat([tiles, flags], 1).contiguous()
 
 
 # ------------------------------------------------------------------ clocks sampler
@@ -155,13 +245,25 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------ CPU baseline (oracle = checker / timed baseline only)
-def _cpu_search_fns(o, ds):
+def _oracle(threads=None):
+    from oracle import tmoracle as o
+    try:
+        o.use_native()
+    except Exception:
+        pass
+    o.set_threads(threads or os.cpu_count() or 1)  # all host cores, whatever OMP_NUM_THREADS the launcher exported
+    return o
+
+
+def _cpu_search_fns(o, ds, k):
     """The two exact CPU variants of BASELINE.md §4: ANN's published kd-tree (bucket 1, standard split,
     eps = 0 — what the reference calls through ANN.dll, main.pas:3961/4027) and a blocked float32 brute
-    force.  Tree / dataset build is one-time per keyframe and not timed (neither is the GPU arm's)."""
+    force (k = 1 only).  Tree / dataset build is one-time per keyframe and not timed (neither is the GPU arm's)."""
     kd = o.KDTreeRef(ds)
-    return {"kdtree": lambda q: tuple(x[:, 0] for x in kd.search(q, 1)),
-            "bruteforce": lambda q: o.nn1_blocked_f32(ds, q)}, kd
+    fns = {"kdtree": lambda q: kd.search(q, k)}
+    if k == 1:
+        fns["bruteforce"] = lambda q: tuple(x.reshape(-1, 1) for x in o.nn1_blocked_f32(ds, q))
+    return fns, kd
 
 
 def _pick_cpu_variant(o, fns, rgb, probe=256):
@@ -176,31 +278,28 @@ def _pick_cpu_variant(o, fns, rgb, probe=256):
     return best
 
 
-def cpu_baseline(tiles_np, pal_np, rgb_sample_np, target_s, check_idx=None, check_err=None):
+def cpu_baseline(tiles_np, pal_np, rgb_sample_np, target_s, k=1, check_idx=None, check_err=None, threads=None,
+                 timed=True):
     """The reference's DoFrameTiling loop (main.pas:4020-4038) restated in C (oracle/), timed on this
     box's host cores on a bounded sample of the same workload; also checks the GPU result on the sample."""
-    from oracle import tmoracle as o
-    try:
-        o.use_native()
-    except Exception:
-        pass
-    o.set_threads(os.cpu_count() or 1)  # all host cores, whatever OMP_NUM_THREADS the launcher exported
+    o = _oracle(threads)
     cores = o.max_threads()
     ds = o.psyv_tileset_f32(tiles_np, pal_np)
-    fns, kd = _cpu_search_fns(o, ds)
-    name, per_q = _pick_cpu_variant(o, fns, rgb_sample_np)
-    n = int(max(256, min(len(rgb_sample_np), target_s / max(per_q, 1e-9))))
+    fns, kd = _cpu_search_fns(o, ds, k)
+    name, per_q = _pick_cpu_variant(o, fns, rgb_sample_np) if timed else ("kdtree", 1.0)
+    n = int(max(256, min(len(rgb_sample_np), target_s / max(per_q, 1e-9)))) if timed else len(rgb_sample_np)
     t0 = time.perf_counter()
     q = o.psyv_queries_f32(rgb_sample_np[:n])
     idx, dist = fns[name](q)
     dt = time.perf_counter() - t0
     out = {"value": n / dt, "unit": "tile-queries/s", "cores": cores, "kind": "port", "variant": name,
-           "sample": f"{n} queries (descriptor + exact 1-NN, {name}, OpenMP over queries) "
+           "sample": f"{n} queries (descriptor + exact {k}-NN, {name}, OpenMP over queries) "
                      f"against the full {ds.shape[0]}-row dataset in {dt:.2f} s; faster of kd-tree / brute force"}
     if check_idx is not None:
         m = min(n, len(check_idx))
-        same = int((idx[:m] == check_idx[:m]).sum())
-        rel = float(np.max(np.abs(dist[:m] - check_err[:m]) / np.maximum(dist[:m], 1e-6)))
+        ci, ce = check_idx[:m].reshape(m, -1), check_err[:m].reshape(m, -1)
+        same = int((idx[:m] == ci).all(1).sum())
+        rel = float(np.max(np.abs(dist[:m] - ce) / np.maximum(dist[:m], 1e-6)))
         out["parity_on_sample"] = {"n": m, "index_equal": same, "max_rel_dist_err": rel}
     kd.close()
     return out
@@ -210,21 +309,48 @@ def run_reference(args, rank, world):
     if rank != 0:
         return
     import torch  # only for the synthetic generator (CPU)
-    frames, pos, ntiles = WORKLOADS[args.workload]
-    gen = torch.Generator(device="cpu").manual_seed(0x42381337)
-    tiles, pal = synth_tileset(torch, ntiles, 16, gen)
-    from oracle import tmoracle as o
-    try:
-        o.use_native()
-    except Exception:
-        pass
-    o.set_threads(os.cpu_count() or 1)  # torchrun exports OMP_NUM_THREADS=1: use all host cores anyway
-    ds = o.psyv_tileset_f32(tiles.numpy(), pal.numpy())
-    cap = 1 << 16
-    rgb = synth_queries(torch, cap, tiles, pal, gen).numpy()
-    fns, kd = _cpu_search_fns(o, ds)
-    name, per_q = _pick_cpu_variant(o, fns, rgb)
+    name_wl = pick_workload(args, world)
+    wl = WORKLOADS[name_wl]
+    o = _oracle()
+    cores = o.max_threads()
     total = args.steps + args.warmup
+    if "points" in wl:  # KModes assignment pass on a bounded sample of the points against all centroids
+        cpu = torch.device("cpu")
+        tiles, _ = lcg_tileset(torch, (BASE_SEED + wl["cfg"]) & M32, 1 << 16, 16, cpu)
+        X = kmodes_rows_torch(torch, tiles).numpy()
+        k = wl["centroids"]
+        cent = np.ascontiguousarray(X[:: len(X) // k][:k]) if len(X) >= k else X
+        n = 2048
+        t0 = time.perf_counter()
+        o.kmodes_assign(X[:n], cent)
+        per = (time.perf_counter() - t0) / n
+        n = int(max(256, min(len(X), (120.0 / max(total, 1)) / max(per, 1e-9))))
+        for _ in range(args.warmup):
+            o.kmodes_assign(X[:n], cent)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            o.kmodes_assign(X[:n], cent)
+        dt = time.perf_counter() - t0
+        v = n * args.steps / dt
+        sample = f"{n} points per step against all {k} centroids (asm-semantics dissimilarity in C, OpenMP over points)"
+        print(json.dumps({
+            "impl": "reference", "metric": "KModes assignment points/sec", "value": v, "unit": "points/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": name_wl, "points_per_step": n, "centroids": k},
+            "cpu_baseline": {"value": v, "unit": "points/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}))
+        return
+    cpu = torch.device("cpu")
+    pal, tiles, qseed = synth_case(torch, wl, cpu)
+    k = wl["k"]
+    pal_np = np.array(pal, np.int32)
+    ds = o.psyv_tileset_f32(tiles.numpy(), pal_np)
+    cap = 1 << 16
+    rgb = lcg_queries(torch, qseed, 0, cap, tiles, pal, cpu)[0].numpy()
+    fns, kd = _cpu_search_fns(o, ds, k)
+    name, per_q = _pick_cpu_variant(o, fns, rgb)
     n = int(max(256, min(cap, (120.0 / max(total, 1)) / max(per_q, 1e-9))))  # whole run <= ~2 min
     for _ in range(args.warmup):
         fns[name](o.psyv_queries_f32(rgb[:n]))
@@ -234,117 +360,308 @@ def run_reference(args, rank, world):
     dt = time.perf_counter() - t0
     kd.close()
     v = n * args.steps / dt
-    cores = o.max_threads()
-    sample = f"{n} queries per step against the full {ds.shape[0]}-row dataset, variant {name}"
+    sample = (f"{n} queries per step (the first {n} of the workload's clip) against the full {ds.shape[0]}-row dataset, "
+              f"k = {k}, variant {name}; CPU cost is linear in the query count")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "tile-queries/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "queries_per_step": n, "dataset_rows": int(ds.shape[0]), "dim": D,
+        "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": name_wl, "queries_per_step": n, "dataset_rows": int(ds.shape[0]), "dim": D, "k": k,
                    "variant": name,
-                   "note": "reference CPU loop (faithful C port of DoFrameTiling: descriptor + exact 1-NN through "
+                   "note": "reference CPU loop (faithful C port of DoFrameTiling: descriptor + exact k-NN through "
                            "ANN's published kd-tree algorithm, or blocked brute force if that is faster here); "
-                           "the FreePascal/ANN.dll original cannot be built on Linux"},
+                           "the FreePascal/ANN.dll original cannot be built on Linux; a SAMPLE of the clip's queries "
+                           "against the full dataset"},
         "cpu_baseline": {"value": v, "unit": "tile-queries/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "tile-queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
 
 # ------------------------------------------------------------------ secondary kernels (reported under `kernels`)
-def helper_kernels(torch, tb, dev, stream, hbm_gbs, reps=3):
-    """Query-descriptor kernel (1 024 B / query), tileset pack (784 B / row) and the KModes assignment
-    pass on BASELINE config 4 (1 048 576 points x 16 384 centroids), CUDA events, best of `reps`."""
-    gen = torch.Generator(device=dev).manual_seed(0x42381337 + 99)
-
-    def timed(fn):
+def _timed(torch, stream, fn, reps=3):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 1e30
+    for _ in range(reps):
+        e0.record(stream)
         fn()
+        e1.record(stream)
         torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        best = 1e30
-        for _ in range(reps):
-            e0.record(stream)
-            fn()
-            e1.record(stream)
-            torch.cuda.synchronize()
-            best = min(best, e0.elapsed_time(e1))
-        return best
+        best = min(best, e0.elapsed_time(e1))
+    return best
 
+
+def kmodes_case(torch, wl, dev):
+    tiles, _ = lcg_tileset(torch, (BASE_SEED + wl["cfg"]) & M32, wl["points"], 16, dev)
+    X = kmodes_rows_torch(torch, tiles)
+    k = wl["centroids"]
+    cent = X[:: wl["points"] // k][:k].contiguous()  # every 64th row (SURVEY.md §8d allows either choice; stated)
+    return X, cent
+
+
+def helper_kernels(torch, tb, dev, stream, hbm_gbs, reps=3):
+    """Query-descriptor kernel (1 024 B / query; 1 420 B with the fused fp16 operand), tileset pack + operand prep
+    (4 688 B per tile) and the KModes assignment pass on BASELINE config 4, CUDA events, best of `reps`."""
     out = {}
-    tiles, pal = synth_tileset(torch, 65536, 16, gen)
+    wl3 = WORKLOADS["c3_1080p_1000f_64k"]
+    pal, tiles, qseed = synth_case(torch, wl3, dev)
+    palt = torch.tensor(pal, dtype=torch.int32, device=dev).view(1, -1)
     nq = 1 << 21
-    rgb = synth_queries(torch, nq, tiles[:4096], pal, gen)
+    rgb, _ = lcg_queries(torch, qseed, 0, nq, tiles, pal, dev)
     desc = torch.empty((nq, 192), dtype=torch.float32, device=dev)
-    ms = timed(lambda: tb.psyv_queries(rgb, out=desc))
+    ms = _timed(torch, stream, lambda: tb.psyv_queries(rgb, out=desc), reps)
     out["psyv_queries"] = {"queries": nq, "ms": ms, "algorithmic_bytes": nq * 1024, "achieved_gbs": nq * 1024 / ms / 1e6,
                            "hbm_frac": nq * 1024 / ms / 1e6 / hbm_gbs}
     del rgb, desc
 
     def create():
-        tb.KDTree.from_tileset(tiles, pal.view(1, -1)).destroy()
-    ms = timed(create)
-    out["tileset_dataset_create"] = {"rows": 262144, "ms": ms,
-                                     "note": "pack/mirror kernel + mean/fp16 operand/norm-tile preparation, C3 tileset"}
-    npnt, k = 1 << 20, 1 << 14
-    t2, _ = synth_tileset(torch, npnt, 16, gen)
-    flags = torch.stack([(t2 == z).sum(1) > 1 for z in range(16)], 1).to(torch.uint8)  # zone flags, main.pas:4142-4165 (S = 16)
-    X = torch.cat([t2, flags], 1).contiguous()
-    cent = X[:: npnt // k][:k].contiguous()
+        tb.KDTree.from_tileset(tiles, palt).destroy()
+    ms = _timed(torch, stream, create, reps)
+    b = wl3["tiles"] * 4688
+    out["tileset_dataset_create"] = {"tiles": wl3["tiles"], "rows": wl3["tiles"] * 4, "ms": ms, "algorithmic_bytes": b,
+                                     "achieved_gbs": b / ms / 1e6, "hbm_frac": b / ms / 1e6 / hbm_gbs,
+                                     "note": "pack/mirror kernel + mean / fp16 operand / norm sort / scan-order copy, C3 "
+                                             "tileset, incl. the host synchronisations of a dataset build"}
+    wl4 = WORKLOADS["c4_kmodes_1m_16k"]
+    X, cent = kmodes_case(torch, wl4, dev)
+    npnt, k = X.shape[0], cent.shape[0]
     clust = torch.empty(npnt, dtype=torch.int32, device=dev)
     dis = torch.empty(npnt, dtype=torch.int64, device=dev)
-    ms = timed(lambda: tb.kmodes_assign(X, cent, tb.KM_ASM, out_clust=clust, out_dis=dis))
+    ms = _timed(torch, stream, lambda: tb.kmodes_assign(X, cent, tb.KM_ASM, out_clust=clust, out_dis=dis), reps)
     b = npnt * 92 + k * 80
     out["kmodes_assign_c4"] = {"points": npnt, "centroids": k, "ms": ms, "pairs_per_s": npnt * k / ms * 1e3,
                                "byte_compares_per_s": npnt * k * 80 / ms * 1e3, "algorithmic_bytes": b,
-                               "achieved_gbs": b / ms / 1e6,
+                               "achieved_gbs": b / ms / 1e6, "hbm_frac": b / ms / 1e6 / hbm_gbs,
                                "bound": "integer ALU (HBM floor %.0f us)" % (b / hbm_gbs / 1e3)}
     return out
 
 
+def call_patterns(torch, tb, tree, d_rgb, pos, cpu_rate=None):
+    """The encoder's real call patterns (main.pas:972, 4027): one frame per tm_frametiling_search call from 8 host
+    threads (pageable memory), and single-query ann_kdtree_search calls from 16 threads."""
+    out = {}
+    nthreads, frames_per_thread = 8, 24
+    frames = [d_rgb[i * pos:(i + 1) * pos].cpu().numpy() for i in range(min(nthreads, d_rgb.shape[0] // pos))]
+    if frames:
+        def worker(i):
+            for _ in range(frames_per_thread):
+                tree.frametiling_search(frames[i % len(frames)])
+        for f in frames:
+            tree.frametiling_search(f)  # warm the per-thread staging paths' device side
+        th = [threading.Thread(target=worker, args=(i,)) for i in range(nthreads)]
+        t0 = time.perf_counter()
+        [t.start() for t in th]
+        [t.join() for t in th]
+        dt = time.perf_counter() - t0
+        ncalls = nthreads * frames_per_thread
+        out["frame_calls"] = {"threads": nthreads, "queries_per_call": pos, "calls": ncalls, "ms_per_call": 1e3 * dt / ncalls,
+                              "queries_per_s": ncalls * pos / dt, "memory": "pageable"}
+    q = tb.psyv_queries(d_rgb[:4096].cpu().numpy())
+    nthreads, per = 16, 256
+
+    def one(i):
+        for j in range(per):
+            tree.search(q[(i * per + j) % len(q)])
+    tree.search(q[0])
+    th = [threading.Thread(target=one, args=(i,)) for i in range(nthreads)]
+    t0 = time.perf_counter()
+    [t.start() for t in th]
+    [t.join() for t in th]
+    dt = time.perf_counter() - t0
+    out["single_query_calls"] = {"threads": nthreads, "calls": nthreads * per, "calls_per_s": nthreads * per / dt,
+                                 "us_per_call": 1e6 * dt / (nthreads * per), "cpu_kdtree_queries_per_s": cpu_rate}
+    return out
+
+
 # ------------------------------------------------------------------ B200 arm
-def run_b200(args, rank, world, local_rank):
+def run_kmodes(args, rank, world, local_rank, name_wl):
+    """--workload c4: the KModes assignment pass, points sharded over the ranks, centroids replicated"""
     import torch
     import torch.distributed as dist
     import tiler_b200 as tb
-
+    wl = WORKLOADS[name_wl]
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     tb.set_device(local_rank)
     stream = torch.cuda.current_stream()
+    tb.set_stream(stream.cuda_stream)
+    X, cent = kmodes_case(torch, wl, dev)
+    from tiler_b200.shard import point_shards
+    a, b = point_shards(X.shape[0], world)[rank]
+    Xl = X[a:b].contiguous()
+    clust = torch.empty(b - a, dtype=torch.int32, device=dev)
+    dis = torch.empty(b - a, dtype=torch.int64, device=dev)
+    gath = torch.empty((world, 3 * (b - a)), dtype=torch.int32, device=dev) if world > 1 else None
+    pack = torch.empty(3 * (b - a), dtype=torch.int32, device=dev) if world > 1 else None
+
+    def step():
+        tb.kmodes_assign(Xl, cent, tb.KM_ASM, out_clust=clust, out_dis=dis)
+        if world > 1:
+            pack[:b - a] = clust
+            pack[b - a:] = dis.view(torch.int32)
+            dist.all_gather_into_tensor(gath, pack)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    tb.reset_stats()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clk:
+        barrier()
+        e0.record(stream)
+        for _ in range(args.steps):
+            step()
+        e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    st = tb.stats()
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    npnt, k = X.shape[0], cent.shape[0]
+    value = npnt * args.steps / (ms / 1e3)
+    # e2e: host buffers through tm_kmodes_assign (H2D of points + centroids, D2H of labels + dissimilarities)
+    Xh, Ch = Xl.cpu().numpy(), cent.cpu().numpy()
+    tb.kmodes_assign(Xh, Ch)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ch, dh = tb.kmodes_assign(Xh, Ch)
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+    if rank == 0:
+        peaks = _peaks()
+        hbm = peaks.get("hbm_gbs") or 6500.0
+        bytes_alg = (b - a) * 92 + k * 80
+        per_launch_ms = ms / args.steps
+        line = {"metric": "KModes assignment points/sec", "value": value, "unit": "points/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic (reference LCG)",
+                "config": {"workload": name_wl, "points": npnt, "centroids": k, "row_bytes": 80,
+                           "parallelism": f"points sharded x{world}, centroids replicated",
+                           "l2_policy": "inputs 84 MB < L2: the pass is integer-ALU bound, not HBM bound (see roofline.note)"},
+                "roofline": {"bound": "hbm", "achieved": bytes_alg / per_launch_ms / 1e6, "peak": hbm, "unit": "GB/s",
+                             "frac": bytes_alg / per_launch_ms / 1e6 / hbm, "traffic": None,
+                             "pairs_per_s": value * k, "byte_compares_per_s": value * k * 80,
+                             "note": "algorithmic bytes = points x 92 + centroids x 80 per launch (timed with the result "
+                                     "all-gather at N > 1); the kernel is integer-pipe bound "
+                                     "(DESIGN.md §4.3): pairs/s is the interpretable figure"},
+                "e2e": {"value": npnt * args.steps / dt, "unit": "points/s", "h2d_bytes_per_step": int((b - a) * 80 + k * 80) * world,
+                        "d2h_bytes_per_step": int((b - a) * 12) * world},
+                "gpu_launches": int(st["kernel_launches"]), "clocks": clk.summary()}
+        if not args.no_cpu_baseline and world == 1:
+            o = _oracle()
+            n = 4096
+            t0 = time.perf_counter()
+            wc, wd = o.kmodes_assign(Xh[:n], Ch)
+            dtc = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": n / dtc, "unit": "points/s", "cores": o.max_threads(), "kind": "port",
+                                    "sample": f"{n} points against all {k} centroids in {dtc:.2f} s",
+                                    "parity_on_sample": {"n": n, "labels_equal": int((wc == ch[:n]).sum()),
+                                                         "dis_equal": int((wd == dh[:n]).sum())}}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def run_b200(args, rank, world, local_rank):
+    name_wl = pick_workload(args, world)
+    if "points" in WORKLOADS[name_wl]:
+        return run_kmodes(args, rank, world, local_rank, name_wl)
+    import torch
+    import torch.distributed as dist
+    import tiler_b200 as tb
+    from tiler_b200.shard import ShardedFrameTiling, frame_shards
+
+    wl = WORKLOADS[name_wl]
+    k = wl["k"]
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    cpu_group = None
+    nccl_init_ms = 0.0
+    if world > 1:
+        t0 = time.perf_counter()
+        dist.init_process_group("nccl", device_id=dev)
+        warm = torch.zeros(1, device=dev)
+        dist.all_reduce(warm)  # communicator bring-up happens here, not inside the tileset broadcast
+        torch.cuda.synchronize()
+        nccl_init_ms = 1e3 * (time.perf_counter() - t0)
+        cpu_group = dist.new_group(backend="gloo")  # host-side barriers that leave the GPUs idle
+    tb.set_device(local_rank)
+    stream = torch.cuda.current_stream()
     tb.set_stream(stream.cuda_stream)  # library work is enqueued on torch's current stream: events see it
     tb.set_engine({"auto": tb.ENGINE_AUTO, "simt": tb.ENGINE_SIMT, "tc": tb.ENGINE_TC}[args.engine])
 
-    frames, pos, ntiles = WORKLOADS[args.workload]
+    frames, pos, ntiles = wl["frames"], wl["pos"], wl["tiles"]
+    sample_note = None
     if args.frames:
         frames = args.frames
-    nq = frames * pos  # per GPU (weak scaling)
-    from tiler_b200.shard import ShardedFrameTiling, frame_shards
-    gen = torch.Generator(device=dev).manual_seed(0x42381337 + (0 if rank == 0 else 977 * rank))
-    tiles, pal = synth_tileset(torch, ntiles, 16, gen)  # ranks > 0 start with a different set: the broadcast decides
-    pal = pal.view(1, -1).contiguous()
+        sample_note = f"--frames {frames} override"
+    elif "sample_frames" in wl:
+        frames = wl["sample_frames"]
+        sample_note = (f"{frames}-frame subsample of the {wl['frames']}-frame clip (the full clip is "
+                       f"{wl['frames'] * pos} queries, {2.0 * wl['frames'] * pos * ntiles * 4 * D:.3g} flop per step)")
+    shards = frame_shards(frames, pos, world)  # strong scaling: the SAME clip cut into contiguous whole-frame shards
+    q0, q1 = shards[rank]
+    nq = q1 - q0
+    nq_total = frames * pos
+    sizes = [b - a for a, b in shards]
+    pal, tiles, qseed = synth_case(torch, wl, dev)
+    if rank != 0:
+        tiles = torch.zeros_like(tiles)  # the broadcast decides
+    palt = torch.tensor(pal if rank == 0 else [0] * 16, dtype=torch.int32, device=dev).view(1, -1).contiguous()
     sft = ShardedFrameTiling()
-    # weak scaling: the clip is `world` times longer, rank r owns the contiguous whole-frame range r
-    shards = frame_shards(frames * world, pos, world)
-    assert shards[rank][1] - shards[rank][0] == nq
     torch.cuda.synchronize()
     t_ds0 = time.perf_counter()
     # one-time tileset broadcast over NCCL/NVLink (SURVEY.md §8e; rank 0's tileset wins), then the
     # pack/mirror kernel + operand prep on every GPU
-    tree = sft.broadcast_tileset(tiles, pal)
+    tree = sft.broadcast_tileset(tiles, palt)
     torch.cuda.synchronize()
     dataset_build_ms = 1e3 * (time.perf_counter() - t_ds0)
-    gen.manual_seed(0x42381337 + 1 + rank)
-    d_rgb = synth_queries(torch, nq, tiles, pal.view(-1), gen)
+    pal = [int(x) for x in palt.view(-1).cpu().tolist()]
+    d_rgb, _ = lcg_queries(torch, qseed, q0, q1, tiles, pal, dev)
+    d_q = None
+    if k > 1:  # C5: the k-NN entry point takes descriptors (UseOne shape); descriptor time is reported separately
+        d_q = torch.empty((nq, D), dtype=torch.float32, device=dev)
+        tb.psyv_queries(d_rgb, out=d_q)
     torch.cuda.synchronize()
-    d_idx = torch.empty(nq, dtype=torch.int32, device=dev)
-    d_err = torch.empty(nq, dtype=torch.float32, device=dev)
-    sizes = [b - a for a, b in shards]
+    m = max(sizes)
+    buf = torch.empty(2 * m * k, dtype=torch.int32, device=dev)  # [idx | err] of this rank: one collective per step
+    d_idx = buf[:nq * k]
+    d_err = buf[m * k:m * k + nq * k].view(torch.float32)
+    gath = torch.empty((world, 2 * m * k), dtype=torch.int32, device=dev) if world > 1 else None
+
+    def search_local():
+        if k == 1:
+            sft.search_local(d_rgb, out_idx=d_idx, out_err=d_err)
+        else:
+            tree.search_batch(d_q, k, out_idx=d_idx, out_err=d_err)
 
     def step():
-        sft.search_local(d_rgb, out_idx=d_idx, out_err=d_err)
-        if world > 1:  # result gather to rank 0 (NCCL) is part of the step
-            sft.gather_results(d_idx, d_err, sizes)
+        search_local()
+        if world > 1:  # result gather (NCCL) is part of the step
+            dist.all_gather_into_tensor(gath, buf)
 
     def barrier():
         torch.cuda.synchronize()
@@ -371,77 +688,179 @@ def run_b200(args, rank, world, local_rank):
     # one more (untimed) pass with the tensor-core engine's error-model audit on: the largest observed coarse-score
     # error over every re-ranked candidate, as a fraction of the bound the certificate assumes (must stay < 1)
     audit = None
-    if local_rank == 0:
+    if rank == 0:
         tb.reset_stats()
         tb.set_profiling(2)
-        sft.search_local(d_rgb, out_idx=d_idx, out_err=d_err)
+        search_local()
         sa = tb.stats()
         tb.set_profiling(False)
-        audit = {"max_observed_over_bound": float(sa["max_error_ratio"]), "candidates": int(sa["audited_candidates"])}
+        audit = {"max_observed_over_bound": float(sa["max_error_ratio"]), "candidates": int(sa["audited_candidates"]),
+                 "candidates_per_query": sa["audited_candidates"] / max(nq, 1)}
     if world > 1:
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    value = world * nq * args.steps / (ms / 1e3)
+    value = nq_total * args.steps / (ms / 1e3)
 
-    # ---- e2e: host buffers through the C ABI, copies inside the timed region
+    # ---- parity of THIS rank's shard against the oracle on a sample (every rank; the minimum is reported)
+    parity = None
+    cpu = None
+    if not args.no_cpu_baseline:
+        msample = 1 << 15 if world == 1 else 2048
+        msample = min(msample, nq)
+        cores = os.cpu_count() or 1
+        cpu = cpu_baseline(tiles.cpu().numpy(), np.array(pal, np.int32), d_rgb[:msample].cpu().numpy(),
+                           args.cpu_seconds, k, d_idx[:msample * k].cpu().numpy(), d_err[:msample * k].cpu().numpy(),
+                           threads=max(1, cores // world), timed=(world == 1))
+        parity = cpu["parity_on_sample"]
+        if world > 1:
+            pt = torch.tensor([parity["n"] - parity["index_equal"], parity["n"]], dtype=torch.float64, device=dev)
+            dist.all_reduce(pt, op=dist.ReduceOp.SUM)
+            pr = torch.tensor([parity["max_rel_dist_err"], 1.0 - parity["index_equal"] / max(parity["n"], 1)],
+                              dtype=torch.float64, device=dev)
+            dist.all_reduce(pr, op=dist.ReduceOp.MAX)
+            parity = {"ranks": world, "n_per_rank": parity["n"], "index_mismatches_all_ranks": int(pt[0].item()),
+                      "worst_rank_index_equal_frac": 1.0 - float(pr[1].item()), "max_rel_dist_err": float(pr[0].item())}
+
+    # ---- e2e, one process per GPU: host buffers through the C ABI, copies inside the timed region
     e2e = None
+    e2e_pp = None
     if not args.no_e2e:
-        h_rgb = torch.empty((nq, 64), dtype=torch.int32, pin_memory=True)
-        h_rgb.copy_(d_rgb)
-        h_idx = torch.empty(nq, dtype=torch.int32, pin_memory=True)
-        h_err = torch.empty(nq, dtype=torch.float32, pin_memory=True)
-        rgb_np, idx_np, err_np = h_rgb.numpy(), h_idx.numpy(), h_err.numpy()
-        e_steps = max(1, min(args.steps, 3))
-        tree.frametiling_search(rgb_np, out_idx=idx_np, out_err=err_np)  # warm-up
+        if k == 1:
+            h_in = torch.empty((nq, 64), dtype=torch.int32, pin_memory=True)
+            h_in.copy_(d_rgb)
+            in_bytes = 256
+        else:
+            h_in = torch.empty((nq, D), dtype=torch.float32, pin_memory=True)
+            h_in.copy_(d_q)
+            in_bytes = 4 * D
+        h_idx = torch.empty(nq * k, dtype=torch.int32, pin_memory=True)
+        h_err = torch.empty(nq * k, dtype=torch.float32, pin_memory=True)
+        in_np, idx_np, err_np = h_in.numpy(), h_idx.numpy(), h_err.numpy()
+
+        def host_call(t, a=in_np, i=idx_np, e=err_np):
+            if k == 1:
+                t.frametiling_search(a, out_idx=i, out_err=e)  # synchronous: returns with results on host
+            else:
+                t.search_batch_into(a, k, i, e)
+        e_steps = max(1, args.steps)
+        host_call(tree)  # warm-up
         barrier()
         t0 = time.perf_counter()
         for _ in range(e_steps):
-            tree.frametiling_search(rgb_np, out_idx=idx_np, out_err=err_np)  # synchronous: returns with results on host
+            host_call(tree)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         if world > 1:
             t = torch.tensor([dt], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        e2e = {"value": world * nq * e_steps / dt, "unit": "tile-queries/s",
-               "h2d_bytes_per_step": int(nq * 256), "d2h_bytes_per_step": int(nq * 8), "steps": e_steps,
-               "timer": "host wall clock around the synchronous C-ABI call, max over ranks"}
+        e2e_pp = {"value": nq_total * e_steps / dt, "unit": "tile-queries/s",
+                  "h2d_bytes_per_step": int(nq_total * in_bytes), "d2h_bytes_per_step": int(nq_total * 8 * k), "steps": e_steps,
+                  "timer": "host wall clock around the synchronous C-ABI call, max over ranks"}
+        e2e = e2e_pp
+
+    extras = {}
+    if rank == 0 and world == 1 and not args.no_extras and k == 1:
+        try:
+            # queries WITHOUT a planted answer in the dataset: rendered from a different tileset (same palette, noise):
+            # the certificate band's worst realistic case - candidates per query and fallbacks reported
+            other, _ = lcg_tileset(torch, (BASE_SEED + 7777) & M32, 4096, 16, dev)
+            nu = min(nq, 1 << 20)
+            u_rgb, _ = lcg_queries(torch, (qseed + 12345) & M32, 0, nu, tiles, pal, dev, unplanted_from=other)
+            ui = torch.empty(nu, dtype=torch.int32, device=dev)
+            ue = torch.empty(nu, dtype=torch.float32, device=dev)
+            tree.frametiling_search(u_rgb, out_idx=ui, out_err=ue)
+            tb.reset_stats()
+            tb.set_profiling(2)
+            tree.frametiling_search(u_rgb, out_idx=ui, out_err=ue)
+            su = tb.stats()
+            tb.set_profiling(False)
+            ms_u = _timed(torch, stream, lambda: tree.frametiling_search(u_rgb, out_idx=ui, out_err=ue), 2)
+            extras["unplanted_queries"] = {
+                "n": nu, "queries_per_s": nu / ms_u * 1e3, "candidates_per_query": su["audited_candidates"] / nu,
+                "fallback_queries": int(su["fallback_queries"]), "max_observed_over_bound": float(su["max_error_ratio"]),
+                "note": "tiles of a different tileset rendered through the palette + noise: no exact answer in the dataset"}
+            if not args.no_cpu_baseline:
+                n_chk = 4096
+                c2 = cpu_baseline(tiles.cpu().numpy(), np.array(pal, np.int32), u_rgb[:n_chk].cpu().numpy(), 1.0, 1,
+                                  ui[:n_chk].cpu().numpy(), ue[:n_chk].cpu().numpy(), timed=False)
+                extras["unplanted_queries"]["parity_on_sample"] = c2["parity_on_sample"]
+            del u_rgb, ui, ue, other
+        except Exception as ex:  # secondary numbers must never cost the headline line
+            extras["unplanted_queries"] = {"error": str(ex)[:200]}
+        try:
+            tb.set_stream(0)
+            extras["call_patterns"] = call_patterns(torch, tb, tree, d_rgb, pos, cpu["value"] if cpu else None)
+            tb.set_stream(stream.cuda_stream)
+        except Exception as ex:
+            extras["call_patterns"] = {"error": str(ex)[:200]}
+
+    kernels = None
+    if rank == 0 and world == 1 and not args.no_kernels:
+        try:
+            kernels = helper_kernels(torch, tb, dev, stream, _peaks().get("hbm_gbs") or 6500.0)
+        except Exception as ex:
+            kernels = {"error": str(ex)[:200]}
+
+    # ---- e2e for N > 1: ONE process (rank 0) drives all N GPUs through the C ABI (tm_set_devices), host buffers
+    single = None
+    if world > 1 and not args.no_e2e:
+        sft.close()
+        tree = None
+        del d_rgb, d_q, buf, gath, d_idx, d_err
+        torch.cuda.empty_cache()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
+        if rank == 0:
+            try:
+                single = single_process_e2e(torch, tb, args, wl, frames, pos, k, world, pal, tiles, qseed, dev)
+            except Exception as ex:
+                single = {"error": str(ex)[:300]}
+        dist.barrier(group=cpu_group)
+        if single and "value" in single:
+            e2e = single
 
     if rank == 0:
         n_rows = ntiles * 4
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
+        peaks = _peaks()
         # dominant kernel = the search; algorithmic flops = 2*Q*N*D per launch
-        search_ms = st["coarse_ms"] if st["coarse_launches"] else st["search_ms"]
-        launches = st["coarse_launches"] if st["coarse_launches"] else max(1, args.steps * ((nq + (1 << 21) - 1) >> 21))
+        search_ms = st["coarse_ms"] if st["coarse_ms"] > 0 else st["search_ms"]
+        launches = int(st["coarse_launches"]) if st["coarse_launches"] else max(1, args.steps)
         flops_total = 2.0 * nq * n_rows * D * args.steps
         achieved = flops_total / (search_ms / 1e3) / 1e12 if search_ms > 0 else None
         # DRAM traffic of one full-size (2 097 152-query) launch of the search kernel, from the committed
         # `ncu --set full` capture (dram__bytes_read.sum + dram__bytes_write.sum); see profiles/README.md
-        traffic = None
+        traffic, traffic_source = None, None
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "tc_search_traffic.json")))
-            if tj["dataset_rows"] == n_rows and nq >= tj["queries_per_launch"]:  # the capture is of this workload's launch
+            if tj["dataset_rows"] == n_rows and nq >= tj["queries_per_launch"] and k == 1:  # the capture is of this workload's launch
                 traffic = tj["dram_bytes_per_launch"]
+                traffic_source = ("profiles/tc_search_traffic.json: committed `ncu --set full` capture of one "
+                                  f"{tj['queries_per_launch']}-query launch of this workload; not measured in this run")
         except Exception:
             pass
         peak = peaks.get("bf16_tflops_sustained") or 1400.0
-        peak_src = "measured sustained (MEASURED_PEAKS.json)" if peaks else "fallback"
+        burst = peaks.get("bf16_tflops") or 1670.0
+        peak_src = "measured sustained cuBLAS bf16 (MEASURED_PEAKS.json)" if peaks else "fallback"
         line = {
             "metric": METRIC, "value": value, "unit": "tile-queries/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong" if world > 1 else "weak",
             "vs_baseline": None, "dtype": "f16 tensor-core coarse pass, f32 exact re-rank" if st["coarse_launches"] else "f32",
-            "data": "synthetic",
-            "config": {"workload": args.workload, "queries_per_gpu": nq, "dataset_rows": n_rows, "dim": D,
-                       "mirrors": 4, "parallelism": f"query-sharded x{world}, tileset replicated",
-                       "l2_policy": "inputs larger than L2 (query RGB %.2f GB per step)" % (nq * 256 / 1e9),
-                       "engine": args.engine, "dataset_build_ms": dataset_build_ms},
+            "data": "synthetic (reference LCG, kmodes.pas:82-86)",
+            "config": {"workload": name_wl, "queries_total": nq_total, "queries_per_gpu": nq, "frames": frames,
+                       "dataset_rows": n_rows, "dim": D, "k": k,
+                       "mirrors": 4, "parallelism": f"query-sharded x{world} (contiguous whole-frame shards), tileset replicated",
+                       "l2_policy": "inputs larger than L2 (query RGB %.2f GB per GPU and step)" % (nq * 256 / 1e9),
+                       "engine": args.engine, "dataset_build_ms": dataset_build_ms, "nccl_init_ms": nccl_init_ms},
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                         "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_source": traffic_source,
+                         "peak_source": peak_src, "peak_burst": burst, "frac_burst": (achieved / burst) if achieved else None,
+                         "peak_note": "the kernel is timed inside a long, power-capped step, so the sustained cuBLAS figure "
+                                      "is the prescribed denominator; it is a library measurement, not a hardware ceiling "
+                                      "(this kernel runs fp16 operands in a 2-CTA schedule cuBLAS' bf16 GEMM does not use), "
+                                      "hence frac can exceed 1: frac_burst is against the burst figure, which does bound it",
                          "kernel": "search (coarse tensor-core pass)" if st["coarse_launches"] else "search (exact SIMT)",
                          "kernel_ms_per_launch": search_ms / launches, "launches": launches,
                          "algorithmic_flops_per_launch": flops_total / launches},
@@ -452,22 +871,77 @@ def run_b200(args, rank, world, local_rank):
             "gpu_launches": int(st["kernel_launches"]),
             "clocks": clk.summary(),
         }
+        if sample_note:
+            line["config"]["sample"] = sample_note
         if e2e:
             line["e2e"] = e2e
-        if args.kernels and world == 1:
-            try:
-                line["kernels"] = helper_kernels(torch, tb, dev, stream, peaks.get("hbm_gbs") or 6500.0)
-            except Exception as e:  # secondary numbers must never cost the headline line
-                line["kernels"] = {"error": str(e)[:200]}
-        if not args.no_cpu_baseline and world == 1:
-            m = 1 << 15
-            line["cpu_baseline"] = cpu_baseline(tiles.cpu().numpy(), pal.view(-1).cpu().numpy(), d_rgb[:m].cpu().numpy(),
-                                                args.cpu_seconds, d_idx[:m].cpu().numpy(), d_err[:m].cpu().numpy())
+        if world > 1 and e2e_pp:
+            line["e2e_process_per_gpu"] = e2e_pp
+        if single and "error" in single:
+            line["e2e_single_process_error"] = single["error"]
+        if kernels:
+            line["kernels"] = kernels
+        line.update(extras)
+        if cpu and world == 1:
+            line["cpu_baseline"] = cpu
+        elif parity:
+            line["parity_on_sample"] = parity
         print(json.dumps(line))
-    sft.close()
+    if tree is not None:
+        sft.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def single_process_e2e(torch, tb, args, wl, frames, pos, k, world, pal, tiles, qseed, dev):
+    """rank 0 only: the whole clip through ONE tm_frametiling_search / ann_kdtree_search_batch call per step, the
+    library sharding it over all `world` GPUs (tm_set_devices): the single-process encoder's view of the box."""
+    nq_total = frames * pos
+    tb.set_stream(0)
+    tb.set_devices(list(range(world)))
+    t0 = time.perf_counter()
+    palt = torch.tensor(pal, dtype=torch.int32, device=dev).view(1, -1)
+    tree = tb.KDTree.from_tileset(tiles, palt)  # built on device 0, replicated over NCCL inside the library
+    build_ms = 1e3 * (time.perf_counter() - t0)
+    in_w = 64 if k == 1 else D
+    h_in = torch.empty((nq_total, in_w), dtype=torch.int32 if k == 1 else torch.float32, pin_memory=True)
+    chunk = 1 << 21
+    for c0 in range(0, nq_total, chunk):  # the clip is generated on GPU 0 in pieces and parked in pinned host memory
+        c1 = min(nq_total, c0 + chunk)
+        rgb, _ = lcg_queries(torch, qseed, c0, c1, tiles, pal, dev)
+        if k == 1:
+            h_in[c0:c1].copy_(rgb)
+        else:
+            dq = torch.empty((c1 - c0, D), dtype=torch.float32, device=dev)
+            tb.psyv_queries(rgb, out=dq)
+            torch.cuda.synchronize()
+            h_in[c0:c1].copy_(dq)
+            del dq
+        del rgb
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    h_idx = torch.empty(nq_total * k, dtype=torch.int32, pin_memory=True)
+    h_err = torch.empty(nq_total * k, dtype=torch.float32, pin_memory=True)
+    a, i, e = h_in.numpy(), h_idx.numpy(), h_err.numpy()
+
+    def call():
+        if k == 1:
+            tree.frametiling_search(a, out_idx=i, out_err=e)
+        else:
+            tree.search_batch_into(a, k, i, e)
+    call()
+    steps = max(1, args.steps)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        call()
+    dt = time.perf_counter() - t0
+    out = {"value": nq_total * steps / dt, "unit": "tile-queries/s", "h2d_bytes_per_step": int(nq_total * in_w * 4),
+           "d2h_bytes_per_step": int(nq_total * 8 * k), "steps": steps, "devices": tb.get_devices(),
+           "replicas": tree.replicas, "library_comm_init_ms": tb.comm_init_ms(), "dataset_build_and_broadcast_ms": build_ms,
+           "timer": "host wall clock around ONE synchronous C-ABI call per step in ONE process driving all GPUs"}
+    tree.destroy()
+    return out
 
 
 def main():

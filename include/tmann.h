@@ -15,11 +15,19 @@
  *
  * Threads: every entry point may be called concurrently from any number of host
  * threads over shared handles, as the encoder does (DoFrameTiling runs one frame
- * per worker thread, main.pas:972).  Device work is serialised on one stream under
- * a process-wide lock; frame-sized tm_frametiling_search calls copy pageable caller
+ * per worker thread, main.pas:972).  Device work is serialised per GPU (one stream,
+ * one lock per device); frame-sized tm_frametiling_search calls copy pageable caller
  * memory through per-thread pinned staging OUTSIDE that lock, so the host copies of
  * one caller overlap the device work of another.  tm_last_error() is per thread.
  * Destroying a handle while another thread still uses it is a caller error.
+ *
+ * Devices: ONE process can drive several GPUs of a box (tm_set_devices, or
+ * TM_DEVICES=all / "0,1,.." in the environment).  A dataset is then built once on
+ * the first device and broadcast to the others over NCCL (NVLink / NVSwitch); the
+ * handle the caller holds stands for all replicas.  Clip-sized host batches are cut
+ * into one contiguous query shard per GPU, every GPU returns its own results into
+ * the caller's buffers; frame-sized and single-query calls go to the least busy GPU,
+ * so the encoder's worker threads spread over the devices without any change.
  */
 #ifndef TMANN_H
 #define TMANN_H
@@ -79,8 +87,19 @@ enum { TM_ENGINE_AUTO = 0, TM_ENGINE_SIMT = 1, TM_ENGINE_TC = 2 };
 
 TM_API const char *tm_last_error(void);
 TM_API int tm_version(void);
-/* Select the CUDA device for the calling process (default: current device). */
+/* Select the CUDA device for the calling process (default: current device, or
+ * TM_DEVICES).  Same as tm_set_devices(&device, 1). */
 TM_API int tm_set_device(int device);
+/* Drive n GPUs from this process: devices[0] builds datasets, all hold replicas.  Brings up
+ * one NCCL communicator over them (libnccl.so.2 is loaded at this point, not before).  May be
+ * called again with another list only while no dataset handle is alive.  The reference fans
+ * DoFrameTiling out over worker threads of ONE process on one shared handle (main.pas:972):
+ * this is what lets that process reach every GPU of the box through the same five imports. */
+TM_API int tm_set_devices(const int *devices, int n);
+/* active device list (returns its length; fills at most cap entries) */
+TM_API int tm_get_devices(int *devices, int cap);
+/* wall time (ms) of the last NCCL communicator bring-up incl. its warm-up broadcast (0: none) */
+TM_API double tm_comm_init_ms(void);
 TM_API int tm_set_engine(int engine);
 /* Run all library work on the caller's CUDA stream (a cudaStream_t).  From then on the
  * *_dev entry points only enqueue work on that stream and return without synchronising;
@@ -99,6 +118,8 @@ TM_API void tm_host_free(void *p);
 TM_API ANNkdtree *tm_dataset_create(const float *rows, int64_t n, int dd, int is_device);
 TM_API int64_t tm_dataset_rows(const ANNkdtree *akd);
 TM_API int tm_dataset_dim(const ANNkdtree *akd);
+/* number of devices holding a replica of this dataset (1 without tm_set_devices) */
+TM_API int tm_dataset_replicas(const ANNkdtree *akd);
 
 /* Batch k-NN: nq queries x dd floats, contiguous; out idxs[nq*k], errs[nq*k]
  * ascending per query.  One call replaces the per-position loop of
@@ -125,8 +146,10 @@ TM_API ANNkdtree *tm_tileset_dataset_create(const uint8_t *h_palpix, int64_t nti
 TM_API ANNkdtree *tm_tileset_dataset_create_dev(const uint8_t *d_palpix, int64_t ntiles,
                                                 const int32_t *d_pals, int npal, int pal_size,
                                                 const uint8_t *d_tile_flags, int flags, int gamma);
-/* copy the dataset rows (float32) back, for inspection / parity tests */
+/* copy the dataset rows (float32) back, for inspection / parity tests; _replica reads the copy
+ * held by the replica-th active device (what the NCCL broadcast delivered) */
 TM_API int tm_dataset_read(const ANNkdtree *akd, float *h_rows);
+TM_API int tm_dataset_read_replica(const ANNkdtree *akd, int replica, float *h_rows);
 
 /* Fused FrameTiling hot loop (main.pas:4020-4038): RGB tiles -> descriptor ->
  * exact 1-NN in akd (dd must be 192).  out row index + squared-L2 err per query,
@@ -143,9 +166,17 @@ TM_API int tm_frametiling_search_dev(ANNkdtree *akd, const int32_t *d_rgb, int64
  * floats in order (none, H, H+V, V); tr_tile / tr_attrs (0,1,3,2) side tables. */
 TM_API ANNkdtree *tm_global_dataset_create(const uint8_t *h_palpix, int64_t ntiles,
                                            int32_t *h_tr_tile, uint8_t *h_tr_attrs);
+/* The same over a tile array with inactive entries (FTiles after MergeTiles and before Reindex):
+ * rows exist for tiles with h_active[t] != 0 only (T^.Active, main.pas:3763-3777), tr_tile holds
+ * indices into the WHOLE array, exactly like TRToTileIdx.  h_active = NULL: every tile is active.
+ * tr_tile / tr_attrs must hold 4 x (number of active tiles) entries; tm_dataset_rows gives that. */
+TM_API ANNkdtree *tm_global_dataset_create_active(const uint8_t *h_palpix, int64_t ntiles,
+                                                  const uint8_t *h_active, int32_t *h_tr_tile,
+                                                  uint8_t *h_tr_attrs);
 
 /* One-call PrepareFrameTiling (main.pas:3791-3967) for a keyframe.  global_ds is the stage-1 handle
- * of tm_global_dataset_create over the same ntiles tiles.  h_item_pal / h_item_tile list the
+ * of tm_global_dataset_create(_active) over the same ntiles tiles (h_palpix is the WHOLE tile array,
+ * inactive tiles included: tilemap items and the used[] table index it, main.pas:3823, 3902).  h_item_pal / h_item_tile list the
  * (PalIdx, GlobalTileIndex) of every tilemap position of the keyframe's frames (duplicates allowed, the
  * "already seen" test of main.pas:3814-3821 is done on the device).  For each distinct pair the 8
  * nearest stage-1 rows of the tile's line are taken (UseOne main.pas:3830; hits with an err equal to the

@@ -129,14 +129,22 @@ static double sq_dist_192(const double *a, const double *b) { /* CompareEuclidea
     return r;
 }
 
-int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int npal,
-                                      const int32_t *item_pal, const int32_t *item_tile, int64_t nitems,
-                                      int quality, double pal_tol, const double *pal_centroids,
-                                      uint8_t *used) {
+/* active: T^.Active per tile (NULL = all).  PrepareGlobalFT (main.pas:3763-3777) emits stage-1 rows for Active
+ * tiles only and records TRToTileIdx; UseOne's query line is FTiles[GlobalTileIndex].PalPixels whatever the
+ * tile's Active flag (3823-3828), and hits are mapped back through TRToTileIdx (3843-3850). */
+int64_t tmo_prepare_frame_tiling_used_active(const uint8_t *palpix, int64_t ntiles, const uint8_t *active, int npal,
+                                             const int32_t *item_pal, const int32_t *item_tile, int64_t nitems,
+                                             int quality, double pal_tol, const double *pal_centroids,
+                                             uint8_t *used) {
     static const uint8_t attrs_of[4] = {0, 1, 3, 2}; /* PrepareGlobalFT row order none,H,HV,V main.pas:3753 */
-    int64_t n = ntiles * 4;
-    float *g = (float *)malloc(sizeof(float) * (size_t)n * 64);
-    tmo_global_rows_f32(palpix, ntiles, g, NULL, NULL);
+    int64_t nact = 0;
+    int32_t *tr_tile = (int32_t *)malloc(sizeof(int32_t) * (size_t)(ntiles ? ntiles : 1));
+    uint8_t *px = (uint8_t *)malloc((size_t)(ntiles ? ntiles : 1) * 64);
+    for (int64_t t = 0; t < ntiles; t++)
+        if (!active || active[t]) { memcpy(px + nact * 64, palpix + t * 64, 64); tr_tile[nact++] = (int32_t)t; }
+    int64_t n = nact * 4;
+    float *g = (float *)malloc(sizeof(float) * (size_t)(n ? n : 1) * 64);
+    tmo_global_rows_f32(px, nact, g, NULL, NULL);
     memset(used, 0, (size_t)npal * ntiles * 4);
     uint8_t *seen = (uint8_t *)calloc((size_t)npal * ntiles, 1);
     double *corr = NULL, highest = 0.0;
@@ -155,14 +163,15 @@ int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int
         if (seen[(size_t)pal * ntiles + tile]) continue;
         seen[(size_t)pal * ntiles + tile] = 1;
         int32_t idxs[8];
-        float errs[8];
-        tmo_knn_f32(g, n, 64, g + (size_t)tile * 4 * 64, 1, 8, idxs, errs); /* Line = the stored tile's PalPixels */
+        float errs[8], line[64];
+        for (int j = 0; j < 64; j++) line[j] = (float)palpix[tile * 64 + j]; /* Line = the stored tile's PalPixels */
+        tmo_knn_f32(g, n, 64, line, 1, 8, idxs, errs);
         float last = INFINITY;
         for (int i = 0; i < 8; i++) {
             if (idxs[i] < 0) break; /* fewer than 8 rows */
             if (errs[i] == last) continue;
             last = errs[i];
-            int64_t t2 = idxs[i] >> 2;
+            int64_t t2 = tr_tile[idxs[i] >> 2];
             int a2 = attrs_of[idxs[i] & 3];
             for (int p = 0; p < npal; p++) {
                 int on = quality == 0 ? (p == pal)
@@ -174,8 +183,16 @@ int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int
     }
     int64_t cnt = 0;
     for (size_t i = 0; i < (size_t)npal * ntiles * 4; i++) cnt += used[i];
-    free(g); free(seen); free(corr);
+    free(g); free(seen); free(corr); free(tr_tile); free(px);
     return cnt;
+}
+
+int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int npal,
+                                      const int32_t *item_pal, const int32_t *item_tile, int64_t nitems,
+                                      int quality, double pal_tol, const double *pal_centroids,
+                                      uint8_t *used) {
+    return tmo_prepare_frame_tiling_used_active(palpix, ntiles, NULL, npal, item_pal, item_tile, nitems, quality, pal_tol,
+                                                pal_centroids, used);
 }
 
 /* DoPsyV main.pas:3883-3919: rows in order pal, tile, vmir, hmir; effective mirror = flag xor tile flag */

@@ -70,6 +70,10 @@ int64_t tmo_prepare_frame_tiling_used(const uint8_t *palpix, int64_t ntiles, int
                                       const int32_t *item_pal, const int32_t *item_tile, int64_t nitems,
                                       int quality, double pal_tol, const double *pal_centroids,
                                       uint8_t *used);
+int64_t tmo_prepare_frame_tiling_used_active(const uint8_t *palpix, int64_t ntiles, const uint8_t *active, int npal,
+                                             const int32_t *item_pal, const int32_t *item_tile, int64_t nitems,
+                                             int quality, double pal_tol, const double *pal_centroids,
+                                             uint8_t *used);
 void tmo_frame_tiling_rows(const uint8_t *used, const uint8_t *palpix, int64_t ntiles, const uint8_t *tile_flags,
                            const int32_t *pals, int npal, int pal_size, int use_wavelets, int gamma,
                            float *rows, int32_t *tr_tile, int32_t *tr_pal, uint8_t *tr_attrs);

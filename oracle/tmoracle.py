@@ -167,7 +167,7 @@ def nn1_blocked_f32(data, q, nthreads=0):
 
 
 def prepare_frame_tiling(palpix, pals, item_pal, item_tile, quality=1, pal_tol=0.05, pal_centroids=None,
-                         tile_flags=None, use_wavelets=True, gamma=-1):
+                         tile_flags=None, use_wavelets=True, gamma=-1, active=None):
     """PrepareFrameTiling (main.pas:3791-3967): returns (rows[KNNSize][192] f32, tr_tile, tr_pal, tr_attrs, used)."""
     palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
     pals = np.ascontiguousarray(pals, np.int32)
@@ -179,10 +179,12 @@ def prepare_frame_tiling(palpix, pals, item_pal, item_tile, quality=1, pal_tol=0
     cen = None if pal_centroids is None else np.ascontiguousarray(pal_centroids, np.float64).reshape(npal, 192)
     tf = None if tile_flags is None else np.ascontiguousarray(tile_flags, np.uint8)
     used = np.zeros((npal, nt, 4), np.uint8)
-    _lib.tmo_prepare_frame_tiling_used.restype = C.c_int64
-    n = _lib.tmo_prepare_frame_tiling_used(_p(palpix, C.c_uint8), i64(nt), int(npal), _p(item_pal, C.c_int32),
-                                           _p(item_tile, C.c_int32), i64(len(item_pal)), int(quality),
-                                           C.c_double(pal_tol), _p(cen, C.c_double), _p(used, C.c_uint8))
+    act = None if active is None else np.ascontiguousarray(active, np.uint8)
+    _lib.tmo_prepare_frame_tiling_used_active.restype = C.c_int64
+    n = _lib.tmo_prepare_frame_tiling_used_active(_p(palpix, C.c_uint8), i64(nt), _p(act, C.c_uint8), int(npal),
+                                                  _p(item_pal, C.c_int32), _p(item_tile, C.c_int32), i64(len(item_pal)),
+                                                  int(quality), C.c_double(pal_tol), _p(cen, C.c_double),
+                                                  _p(used, C.c_uint8))
     rows = np.empty((n, 192), np.float32)
     tr_tile = np.empty(n, np.int32)
     tr_pal = np.empty(n, np.int32)

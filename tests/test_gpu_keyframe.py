@@ -96,3 +96,39 @@ def test_keyframe_bad_arguments(tb, oracle):
         t = g.keyframe_dataset(tiles, pals, item_pal[:0], item_tile[:0], quality=0)  # empty keyframe
         assert t.n == 0
         t.destroy()
+
+
+@pytest.mark.parametrize("quality", [0, 1])
+def test_keyframe_dataset_with_inactive_tiles(tb, oracle, quality):
+    """FTiles with inactive entries (after MergeTiles, before Reindex): PrepareGlobalFT emits stage-1 rows for Active
+    tiles only and maps hits back through TRToTileIdx (main.pas:3763-3777, 3843-3850); tilemap items and the used[]
+    table keep indexing the whole tile array."""
+    o = oracle
+    pals, tiles, flags, item_pal, item_tile, cen = _case(o, ntiles=400, seed=33)
+    rng = np.random.default_rng(5)
+    active = (rng.random(400) < 0.6).astype(np.uint8)
+    active[[3, 4]] = 1
+    active[5] = 0                                  # the duplicate of tile 4 is inactive: it may be queried, never hit
+    item_tile = item_tile.copy()
+    rows, tt, tp, ta, used = o.prepare_frame_tiling(tiles, pals, item_pal, item_tile, quality=quality, pal_tol=0.05,
+                                                    pal_centroids=cen, tile_flags=flags, active=active)
+    assert not used[:, active == 0].any()          # inactive tiles never enter the stage-2 dataset
+    g, tr_tile, tr_attrs = tb.KDTree.global_ft(tiles, active=active)
+    assert g.n == 4 * int(active.sum())
+    assert np.array_equal(tr_tile, np.repeat(np.flatnonzero(active), 4))
+    assert np.array_equal(tr_attrs, np.tile(np.array([0, 1, 3, 2], np.uint8), int(active.sum())))
+    want_rows, _, _ = o.global_rows_f32(tiles[active != 0])
+    with g:
+        assert np.array_equal(g.rows(), want_rows)
+        t = g.keyframe_dataset(tiles, pals, item_pal, item_tile, quality=quality, pal_tol=0.05, pal_centroids=cen,
+                               tile_flags=flags)
+        with t:
+            assert t.n == len(rows), (t.n, len(rows))
+            assert np.array_equal(t.attrs["tr_tile"], tt)
+            assert np.array_equal(t.attrs["tr_pal"], tp)
+            assert np.array_equal(t.attrs["tr_attrs"], ta)
+            assert np.array_equal(t.rows(), rows)
+    # all-active mask == no mask
+    g2, tr2, _ = tb.KDTree.global_ft(tiles, active=np.ones(400, np.uint8))
+    with g2:
+        assert g2.n == 1600 and np.array_equal(tr2, np.repeat(np.arange(400), 4))

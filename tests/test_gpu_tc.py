@@ -47,10 +47,42 @@ def test_tc_equals_simt_psyv(tb, oracle, ntiles, nq, k):
         si, se, ti, te, st = _both(tb, t, q, k)
     assert np.array_equal(si, ti)
     assert np.array_equal(se.view(np.uint32), te.view(np.uint32))
-    assert st["coarse_launches"] == 0 or True
+    assert st["coarse_launches"] > 0, st  # counted unconditionally: the tcgen05 kernel ran, not the exact engine
     assert st["fallback_queries"] < 0.2 * nq, st  # the coarse pass must certify the bulk
     oi, od = o.knn_f32(ds, q, k)
     assert np.array_equal(te.view(np.uint32), od.view(np.uint32))
+
+
+@pytest.mark.parametrize("dd,k", [(96, 1), (128, 1), (128, 8), (64, 1), (80, 4), (192, 8)])
+def test_tc_every_operand_width(tb, oracle, dd, k):
+    """NCH = 1 (dd <= 64), 2 (64 < dd <= 128) and 3 (128 < dd <= 192) instantiations of the kernel, padded operand
+    rows included (dd = 80, 96: kp = 128); the forced tensor-core engine must have launched and must equal the exact
+    engine bit for bit."""
+    rng = np.random.default_rng(1000 + dd + k)
+    ds = rng.standard_normal((9000, dd)).astype(np.float32)
+    q = (ds[rng.integers(0, 9000, 2500)] + 0.1 * rng.standard_normal((2500, dd))).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        si, se, ti, te, st = _both(tb, t, q, k)
+    assert st["coarse_launches"] > 0, st
+    assert np.array_equal(si, ti) and np.array_equal(se.view(np.uint32), te.view(np.uint32))
+    oi, od = oracle.knn_f32(ds, q[:64], k)
+    assert np.array_equal(te[:64].view(np.uint32), od.view(np.uint32))
+
+
+def test_tc_envelope_is_visible_in_the_counters(tb):
+    """k > 8 and datasets wider than 192 are outside the tensor-core path: the exact engine answers, and the
+    launch counter says so (no silent substitution inside a 'tensor-core' test)."""
+    rng = np.random.default_rng(3)
+    ds = rng.standard_normal((2000, 192)).astype(np.float32)
+    q = rng.standard_normal((300, 192)).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        tb.reset_stats()
+        tb.set_engine(tb.ENGINE_TC)
+        t.search_batch(q, k=12)
+        assert tb.stats()["coarse_launches"] == 0
+        t.search_batch(q, k=8)
+        assert tb.stats()["coarse_launches"] > 0
+        tb.set_engine(tb.ENGINE_AUTO)
 
 
 def test_tc_random_gaussian_hard_case(tb, oracle):
@@ -206,6 +238,7 @@ def test_tc_long_items_equal_exact_engine(tb, oracle, k):
     q[:512] = ds[:2048:4][:512] + (1e-3 * rng.standard_normal((512, 192))).astype(np.float32)  # answers inside the seed tiles
     with tb.KDTree.from_rows(ds) as t:
         si, se, ti, te, st = _both(tb, t, q, k)
+    assert st["coarse_launches"] > 0, st
     assert np.array_equal(se.view(np.uint32), te.view(np.uint32))
     assert np.array_equal(si, ti)
     assert st["fallback_queries"] < nq // 20, st

@@ -36,6 +36,12 @@ PROTOTYPES = {
     "tm_last_error": (C.c_char_p, []),
     "tm_version": (i32, []),
     "tm_set_device": (i32, [i32]),
+    "tm_set_devices": (i32, [vp, i32]),
+    "tm_get_devices": (i32, [vp, i32]),
+    "tm_comm_init_ms": (C.c_double, []),
+    "tm_dataset_replicas": (i32, [vp]),
+    "tm_dataset_read_replica": (i32, [vp, i32, vp]),
+    "tm_global_dataset_create_active": (vp, [vp, i64, vp, vp, vp]),
     "tm_set_engine": (i32, [i32]),
     "tm_set_stream": (i32, [vp]),
     "tm_device_sync": (i32, []),

@@ -32,6 +32,25 @@ def set_device(dev):
     check(lib.tm_set_device(int(dev)))
 
 
+def set_devices(devs):
+    """Drive several GPUs from this process (tm_set_devices): datasets are built on devs[0] and broadcast over NCCL."""
+    devs = [int(d) for d in devs]
+    arr = (C.c_int * len(devs))(*devs)
+    check(lib.tm_set_devices(arr, len(devs)))
+
+
+def get_devices():
+    arr = (C.c_int * 16)()
+    n = lib.tm_get_devices(arr, 16)
+    if n < 0:
+        check(n)
+    return [int(arr[i]) for i in range(n)]
+
+
+def comm_init_ms():
+    return float(lib.tm_comm_init_ms())
+
+
 def set_engine(engine):
     check(lib.tm_set_engine(int(engine)))
 
@@ -98,13 +117,15 @@ class KDTree:
         return cls(h)
 
     @classmethod
-    def global_ft(cls, palpix):
-        """PrepareGlobalFT (main.pas:3736-3780): returns (tree, TRToTileIdx, TRToAttrs)."""
+    def global_ft(cls, palpix, active=None):
+        """PrepareGlobalFT (main.pas:3736-3780): returns (tree, TRToTileIdx, TRToAttrs).
+        active: optional bool/uint8 [ntiles] = T^.Active (rows only for active tiles, main.pas:3763-3777)."""
         palpix = np.ascontiguousarray(palpix, np.uint8).reshape(-1, 64)
-        n = palpix.shape[0] * 4
+        act = None if active is None else np.ascontiguousarray(active, np.uint8)
+        n = (palpix.shape[0] if act is None else int((act != 0).sum())) * 4
         tr_tile = np.empty(n, np.int32)
         tr_attrs = np.empty(n, np.uint8)
-        h = lib.tm_global_dataset_create(_hp(palpix), palpix.shape[0], _hp(tr_tile), _hp(tr_attrs))
+        h = lib.tm_global_dataset_create_active(_hp(palpix), palpix.shape[0], _hp(act), _hp(tr_tile), _hp(tr_attrs))
         return cls(h), tr_tile, tr_attrs
 
     def keyframe_dataset(self, palpix, pals, item_pal, item_tile, quality=1, pal_tol=0.05, pal_centroids=None,
@@ -151,9 +172,13 @@ class KDTree:
     def dd(self):
         return int(lib.tm_dataset_dim(self._h))
 
-    def rows(self):
+    @property
+    def replicas(self):
+        return int(lib.tm_dataset_replicas(self._h))
+
+    def rows(self, replica=0):
         out = np.empty((self.n, self.dd), np.float32)
-        check(lib.tm_dataset_read(self._h, _hp(out)))
+        check(lib.tm_dataset_read_replica(self._h, int(replica), _hp(out)))
         return out
 
     # -- legacy single-query entry points (extern.pas:65-67) ----------------------
@@ -186,6 +211,11 @@ class KDTree:
         err = np.empty((q.shape[0], k), np.float32)
         check(lib.ann_kdtree_search_batch(self._h, _hp(q), q.shape[0], k, _hp(idx), _hp(err)))
         return idx, err
+
+    def search_batch_into(self, q, k, out_idx, out_err):
+        """ann_kdtree_search_batch with caller-owned (e.g. pinned) host buffers: no allocation, no copy in Python"""
+        check(lib.ann_kdtree_search_batch(self._h, _hp(q), q.shape[0], int(k), _hp(out_idx), _hp(out_err)))
+        return out_idx, out_err
 
     def frametiling_search(self, rgb, wavelets=True, gamma=-1, out_idx=None, out_err=None):
         """DoFrameTiling hot loop (main.pas:4020-4038) for a batch of RGB tiles."""

@@ -16,7 +16,8 @@ namespace {
 
 __global__ void kf_mark_kernel(const int32_t *__restrict__ item_pal, const int32_t *__restrict__ item_tile,
                                int64_t nitems, int64_t ntiles, int npal, const int *__restrict__ knn_idx,
-                               const float *__restrict__ knn_err, const uint8_t *__restrict__ palmask,
+                               const float *__restrict__ knn_err, const int32_t *__restrict__ tr_tile,
+                               const uint8_t *__restrict__ palmask,
                                uint32_t *__restrict__ seen, uint8_t *__restrict__ used, int *__restrict__ bad) {
     const int64_t it = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (it >= nitems) return;
@@ -35,11 +36,18 @@ __global__ void kf_mark_kernel(const int32_t *__restrict__ item_pal, const int32
         const float e = knn_err[tile * 8 + i];
         if (e == last) continue; // main.pas:3835-3837
         last = e;
-        const int64_t t2 = idx >> 2;
+        // stage-1 rows exist for Active tiles only (PrepareGlobalFT main.pas:3763-3777): TRToTileIdx maps back
+        const int64_t t2 = tr_tile ? tr_tile[idx >> 2] : idx >> 2;
         const int a2 = (0x2310 >> ((idx & 3) * 4)) & 3; // row order none,H,HV,V -> attrs 0,1,3,2 (main.pas:3753)
         for (int p = 0; p < npal; p++)
             if (mask[p]) used[((int64_t)p * ntiles + t2) * 4 + a2] = 1;
     }
+}
+
+// UseOne's query line: the stored tile's 64 palette indices as floats (main.pas:3823-3828)
+__global__ void kf_lines_kernel(const uint8_t *__restrict__ palpix, int64_t n, float *__restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (float)palpix[i];
 }
 
 struct ByteToInt {
@@ -65,12 +73,20 @@ __global__ void kf_tables_kernel(const int64_t *__restrict__ row_map, int64_t nr
 
 } // namespace
 
+int tm_launch_kf_lines(const uint8_t *d_palpix, int64_t ntiles, float *d_lines, cudaStream_t s) {
+    if (ntiles == 0) return 0;
+    const int64_t n = ntiles * 64;
+    kf_lines_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d_palpix, n, d_lines);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "kf_lines_kernel");
+}
+
 int tm_launch_kf_mark(const int32_t *d_item_pal, const int32_t *d_item_tile, int64_t nitems, int64_t ntiles, int npal,
-                      const int *d_knn_idx, const float *d_knn_err, const uint8_t *d_palmask, uint32_t *d_seen,
-                      uint8_t *d_used, int *d_bad, cudaStream_t s) {
+                      const int *d_knn_idx, const float *d_knn_err, const int32_t *d_tr_tile, const uint8_t *d_palmask,
+                      uint32_t *d_seen, uint8_t *d_used, int *d_bad, cudaStream_t s) {
     if (nitems == 0) return 0;
     kf_mark_kernel<<<(unsigned)((nitems + 255) / 256), 256, 0, s>>>(d_item_pal, d_item_tile, nitems, ntiles, npal, d_knn_idx,
-                                                                   d_knn_err, d_palmask, d_seen, d_used, d_bad);
+                                                                   d_knn_err, d_tr_tile, d_palmask, d_seen, d_used, d_bad);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "kf_mark_kernel");
 }

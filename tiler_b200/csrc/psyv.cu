@@ -493,8 +493,8 @@ struct PsyvDeviceState {
     double *qw = nullptr;                             // 192 Q weights
     int device = -1;
     bool linear_ok = false; // the arithmetic c / 255.0 matched the table for all 256 values
-    std::mutex mu;
-} g_ps;
+} g_ps_dev[TM_MAX_DEV]; // one table set per device; callers hold that device's lock
+#define g_ps (g_ps_dev[tm_dev()->device])
 
 const int q_luma[64] = {16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55,
                         14, 13, 16, 24, 40, 57, 69, 56, 14, 17, 22, 29, 51, 87, 80, 62,
@@ -506,9 +506,7 @@ const int q_chroma[64] = {17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99
                           99, 99, 112, 128, 144, 160, 176, 192, 99, 112, 128, 144, 160, 176, 192, 208};
 
 int ensure_tables() {
-    std::lock_guard<std::mutex> lk(g_ps.mu);
-    int dev;
-    TM_CUDA(cudaGetDevice(&dev));
+    const int dev = tm_dev()->device;
     if (g_ps.device == dev && g_ps.lut) return 0;
     static const double gam[2] = {2.0, 0.6}; // main.pas:586
     {   // the kernels' table-free evaluation of c / 255.0 (channel_value), replayed on the host
@@ -587,13 +585,12 @@ int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, 
     PsyvConsts K = make_consts();
     unsigned grid = (unsigned)((nq + PQ_TILES - 1) / PQ_TILES);
     const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
-    static bool attr = false;
-    if (!attr) {
+    static std::atomic<uint32_t> attr{0}; // per device (tm_first_on_device)
+    if (tm_first_on_device(attr)) {
         TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
         TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
         TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
         TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
-        attr = true;
     }
     const bool linear = gamma < 0 && g_ps.linear_ok; // GammaCor = -1: c / 255.0 without the table
     const bool wav = (flags & TM_PSYV_WAVELETS) != 0;
@@ -660,10 +657,9 @@ int tm_launch_temporal_smoothing(const uint8_t *d_palpix, int64_t ntiles, const 
     if (nframes == 0 || npos == 0) return 0;
     int r = ensure_tables();
     if (r) return r;
-    static bool attr = false;
-    if (!attr) {
+    static std::atomic<uint32_t> attr{0}; // per device (tm_first_on_device)
+    if (tm_first_on_device(attr)) {
         TM_CUDA(cudaFuncSetAttribute(temporal_smoothing_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TS_SMEM));
-        attr = true;
     }
     const int64_t blocks = (npos + TS_WARPS - 1) / TS_WARPS;
     const unsigned grid = (unsigned)(blocks < 148 * 8 ? blocks : 148 * 8);

@@ -45,8 +45,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// Bounded: a slip in a barrier protocol becomes a trapped kernel (an error code on the host) instead of a hung
+// GPU.  try_wait suspends the thread for a hardware-defined time per attempt, so 2^28 failed attempts are tens of
+// seconds at the least - far beyond any wait of a correct run (the longest kernel here runs < 1 s).
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 28)) __trap();
     }
 }
 

@@ -196,14 +196,13 @@ int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, 
     const bool staged = (dd & 3) == 0 && (((uintptr_t)d_q | (uintptr_t)d_rows) & 15) == 0;
     const int maxv = nsplit * kc > RR_MAXV ? RR_MAXV_WIDE : RR_MAXV;
     const size_t dyn = (size_t)maxv * RR_THREADS;
-    static bool attr = false;
-    if (!attr) {
+    static std::atomic<uint32_t> attr{0}; // per device (tm_first_on_device)
+    if (tm_first_on_device(attr)) {
         const int wide = RR_MAXV_WIDE * RR_THREADS;
         TM_CUDA(cudaFuncSetAttribute(rerank_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
         TM_CUDA(cudaFuncSetAttribute(rerank_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
         TM_CUDA(cudaFuncSetAttribute(rerank_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
         TM_CUDA(cudaFuncSetAttribute(rerank_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
-        attr = true;
     }
 #define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, dyn, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, d_qdnorm, max_tnorm, max_dnorm, k, maxv, d_idx, d_err, d_fb_list, d_fb_count, tm_audit_slots())
     if (k == 1) { if (staged) RR_LAUNCH(true, true); else RR_LAUNCH(true, false); }

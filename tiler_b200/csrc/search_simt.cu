@@ -155,12 +155,7 @@ __global__ void simt_merge_kernel(const float *__restrict__ part_d, const int *_
         }
 }
 
-struct Scratch {
-    float *d = nullptr;
-    int *i = nullptr;
-    size_t cap = 0;
-    std::mutex mu;
-} g_scratch;
+#define g_scratch (tm_dev()->simt) // split-merge scratch of the calling thread's device (device lock held)
 
 template <int K>
 int run(const float *rows, int64_t n, int dd, const float *q, const int *qlist, int64_t nq, int k, int *idx,
@@ -169,11 +164,9 @@ int run(const float *rows, int64_t n, int dd, const float *q, const int *qlist, 
     size_t smem = (size_t)2 * TQ * (ddp + 4) * sizeof(float);
     size_t smem_merge = (size_t)TQ * 16 * K * 8;
     if (smem_merge > smem) smem = smem_merge;
-    static bool attr_set[64] = {};
-    if (!attr_set[K]) {
+    static std::atomic<uint32_t> attr_set{0}; // per template instance and device
+    if (tm_first_on_device(attr_set))
         TM_CUDA(cudaFuncSetAttribute(simt_knn_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set[K] = true;
-    }
     int64_t qblocks = (nq + TQ - 1) / TQ;
     int64_t tiles = (n + TR - 1) / TR;
     int target = 2 * tm_num_sms();
@@ -186,10 +179,9 @@ int run(const float *rows, int64_t n, int dd, const float *q, const int *qlist, 
     if (rows_per_split < TR) rows_per_split = TR;
     splits = (n + rows_per_split - 1) / rows_per_split;
     if (splits < 1) splits = 1;
-    std::lock_guard<std::mutex> lk(g_scratch.mu);
     size_t need = (size_t)nq * splits * K;
     if (need > g_scratch.cap) {
-        if (g_scratch.d) { cudaFree(g_scratch.d); cudaFree(g_scratch.i); }
+        if (g_scratch.d) { cudaStreamSynchronize(s); cudaFree(g_scratch.d); cudaFree(g_scratch.i); g_scratch.d = nullptr; g_scratch.cap = 0; }
         TM_CUDA(cudaMalloc(&g_scratch.d, need * sizeof(float)));
         TM_CUDA(cudaMalloc(&g_scratch.i, need * sizeof(int)));
         g_scratch.cap = need;

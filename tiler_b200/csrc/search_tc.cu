@@ -6,12 +6,12 @@
 // Coarse pass.  Rows and queries are centred on the dataset's column mean (distance-
 // invariant) and rounded to fp16; the kernel computes, for every (query, row),
 //     s~ = ||t~||^2 - 2 q~.t~  =  ||q~ - t~||^2 - ||q~||^2
-// as a dense contraction on the 5th-gen tensor cores: a persistent, warp-specialised CTA
-// per SM keeps a 256-query tile resident in shared memory (two M = 128 halves), streams
-// 128-row tileset tiles through a 6-deep TMA ring, issues tcgen05.mma (M128 N128 K16,
-// fp32 accumulate) into four TMEM accumulators (2 halves x 2 stages = 512 columns), and
-// eight epilogue warps read them back with tcgen05.ld (thread = query row) and keep each
-// query's KC smallest scores in registers.  The Q x N score matrix never reaches HBM.
+// as a dense contraction on the 5th-gen tensor cores.  The kernel (search_tc2_kernel.inc) runs as persistent
+// clusters of two CTAs: each CTA keeps 128 queries resident in shared memory and streams ITS 128 rows of every
+// 256-row tileset tile through an 8-deep TMA ring; the leader issues tcgen05.mma.cta_group::2 (M256 N256 K16,
+// fp32 accumulate) into two TMEM accumulator stages (2 x 256 columns), and eight epilogue warps per CTA read them
+// back with tcgen05.ld (thread = query row, warp = lane quarter x column half) and keep each query's best rows.
+// The Q x N score matrix never reaches HBM.
 //
 // Scan order (k = 1).  The CTA-pair kernel's k = 1 variant does not spend an MMA on ||t~||^2 (1/13 of the tensor
 // time): its accumulator holds -2 q~.t~ only, and the epilogue's fast path tests
@@ -26,8 +26,9 @@
 //
 // Exactness.  s~ + ||q~||^2 is the exact squared distance between the ROUNDED vectors up to
 // fp32 summation error, so by the triangle inequality every row that is not a candidate
-// has true distance >= (sqrt(tau + ||q~||^2 - a) - e)^2 with tau the largest kept score,
-// e = 2^-11 (||q'|| + max||t'||) + tiny and a the accumulation slack.  rerank.cu recomputes
+// has true distance >= (sqrt(tau + ||q~||^2 - a) - e)^2 with tau the final admission threshold,
+// e = ||q~ - q16|| + max ||t~ - t16|| (both MEASURED: per query by the operand code, per dataset at build) and a the
+// fp32 accumulation slack (search_tc.h states the model and its assumption).  rerank.cu recomputes
 // the candidates in exact float32 (the reference's arithmetic), and queries whose k-th
 // best exact distance is not strictly below that bound are re-run on the exact SIMT
 // engine.  Results are therefore identical to the SIMT engine's, not approximately equal.
@@ -218,22 +219,42 @@ int make_tmap_norm(CUtensorMap *m, const __half *base, int64_t tiles) {
 
 } // namespace
 
+namespace {
+struct TmpBuf { // stream-ordered temporary, released on every return path
+    void *p = nullptr;
+    ~TmpBuf() { tm_dev_free(p); }
+    template <class T> T *as() { return static_cast<T *>(p); }
+    void *release() { void *q = p; p = nullptr; return q; }
+};
+} // namespace
+
+// (re)build the TMA descriptors of a handle whose operand buffers exist on the calling thread's device
+int tm_dataset_tensor_maps(ANNkdtree *h) {
+    if (!h->tmap_rows) h->tmap_rows = malloc(3 * sizeof(CUtensorMap)); // [0] rows_f16, [1] norm tiles, [2] rows_f16s (k = 1 scan order)
+    int r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows), h->rows_f16, h->n_pad, h->kp);
+    if (!r) r = make_tmap_norm(static_cast<CUtensorMap *>(h->tmap_rows) + 1, h->norm_tiles, h->n_pad / 128);
+    if (!r) r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows) + 2, h->rows_f16s, h->n_pad, h->kp);
+    return r;
+}
+
 // Called at dataset creation (rows_f32 already queued on s).  Leaves rows_f16 == nullptr when
 // the tensor-core path does not apply (dd > 192, empty set, values outside the fp16 range).
+// On an error return the caller frees the handle (and with it whatever was attached to it here).
 int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     h->rows_f16 = nullptr;
     if (h->n < 1 || h->dd > 192) return 0;
     const int kp = ((h->dd + 63) / 64) * 64;
     const int64_t n_pad = ((h->n + 255) / 256) * 256; // whole 256-row tiles of the CTA-pair kernel
     const int nblocks = (int)((h->n + PREP_ROWS - 1) / PREP_ROWS);
-    double *part = nullptr;
-    unsigned int *mx = nullptr;
-    __half *r16 = nullptr;
-    TM_CUDA(tm_dev_malloc(&part, sizeof(double) * (size_t)nblocks * h->dd));
-    TM_CUDA(tm_dev_malloc(&mx, 4 * sizeof(unsigned int)));
+    TmpBuf part_b, mx_b, r16_b;
+    TM_CUDA(tm_dev_malloc_raw(&part_b.p, sizeof(double) * (size_t)nblocks * h->dd));
+    TM_CUDA(tm_dev_malloc_raw(&mx_b.p, 4 * sizeof(unsigned int)));
     TM_CUDA(tm_dev_malloc(&h->mean, sizeof(float) * h->dd));
     TM_CUDA(tm_dev_malloc(&h->norms, sizeof(float) * n_pad));
-    TM_CUDA(tm_dev_malloc(&r16, sizeof(__half) * (size_t)n_pad * kp));
+    TM_CUDA(tm_dev_malloc_raw(&r16_b.p, sizeof(__half) * (size_t)n_pad * kp));
+    double *part = part_b.as<double>();
+    unsigned int *mx = mx_b.as<unsigned int>();
+    __half *r16 = r16_b.as<__half>();
     TM_CUDA(cudaMemsetAsync(mx, 0, 4 * sizeof(unsigned int), s));
     colsum_partial_kernel<<<nblocks, 192, 0, s>>>(h->rows_f32, h->n, h->dd, part);
     colmean_final_kernel<<<h->dd, 128, 0, s>>>(part, nblocks, h->n, h->dd, h->mean);
@@ -244,8 +265,6 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     unsigned int hmx[4];
     TM_CUDA(cudaMemcpyAsync(hmx, mx, sizeof hmx, cudaMemcpyDeviceToHost, s));
     TM_CUDA(cudaStreamSynchronize(s));
-    tm_dev_free(part);
-    tm_dev_free(mx);
     float max_norm, max_abs;
     memcpy(&max_norm, &hmx[0], 4);
     memcpy(&max_abs, &hmx[1], 4);
@@ -254,37 +273,33 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
     // norm scale S (power of two, representable in fp16) so that ||t~||^2 / S fits fp16
     float S = 1.f;
     while (max_n16 / S > 32768.f && S < 32768.f) S *= 2.f;
-    if (!(max_abs < 30000.f) || !(max_n16 / S < 60000.f)) { // outside the fp16 envelope (or NaN): exact engine only
-        tm_dev_free(r16);
-        return 0;
-    }
+    if (!(max_abs < 30000.f) || !(max_n16 / S < 60000.f)) return 0; // outside the fp16 envelope (or NaN): exact engine only
     TM_CUDA(tm_dev_malloc(&h->norm_tiles, (size_t)(n_pad / 128) * 4096));
     normtile_kernel<<<(unsigned)((n_pad + 255) / 256), 256, 0, s>>>(h->norms, n_pad, 1.f / S, h->norm_tiles);
     tm_count_launch();
     TM_CUDA(cudaGetLastError());
     h->norm_scale = S;
-    h->rows_f16 = r16;
     h->n_pad = n_pad;
     h->kp = kp;
     h->max_norm = max_norm;
     memcpy(&h->max_dnorm, &hmx[3], 4);
     {   // k = 1 scan order (header comment): stable sort by ||t~||^2 - non-negative floats order like their bit
         // patterns, +inf padding last - then rows / norms / perm gathered tile by tile
-        uint32_t *k1 = nullptr;
-        int *v0 = nullptr, *v1 = nullptr;
-        void *tmp = nullptr;
+        TmpBuf k1_b, v0_b, v1_b, tmp_b;
         size_t tmp_bytes = 0;
-        TM_CUDA(tm_dev_malloc(&k1, sizeof(uint32_t) * n_pad));
-        TM_CUDA(tm_dev_malloc(&v0, sizeof(int) * n_pad));
-        TM_CUDA(tm_dev_malloc(&v1, sizeof(int) * n_pad));
+        TM_CUDA(tm_dev_malloc_raw(&k1_b.p, sizeof(uint32_t) * n_pad));
+        TM_CUDA(tm_dev_malloc_raw(&v0_b.p, sizeof(int) * n_pad));
+        TM_CUDA(tm_dev_malloc_raw(&v1_b.p, sizeof(int) * n_pad));
         TM_CUDA(tm_dev_malloc(&h->norms_s, sizeof(float) * n_pad));
         TM_CUDA(tm_dev_malloc(&h->perm, sizeof(int) * n_pad));
         TM_CUDA(tm_dev_malloc(&h->rows_f16s, sizeof(__half) * (size_t)n_pad * kp));
+        uint32_t *k1 = k1_b.as<uint32_t>();
+        int *v0 = v0_b.as<int>(), *v1 = v1_b.as<int>();
         const uint32_t *k0 = reinterpret_cast<const uint32_t *>(h->norms);
         iota_kernel<<<(unsigned)((n_pad + 255) / 256), 256, 0, s>>>(v0, n_pad);
         TM_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, k0, k1, v0, v1, (int)n_pad, 0, 32, s));
-        TM_CUDA(tm_dev_malloc_raw(&tmp, tmp_bytes ? tmp_bytes : 4));
-        TM_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, k0, k1, v0, v1, (int)n_pad, 0, 32, s));
+        TM_CUDA(tm_dev_malloc_raw(&tmp_b.p, tmp_bytes ? tmp_bytes : 4));
+        TM_CUDA(cub::DeviceRadixSort::SortPairs(tmp_b.p, tmp_bytes, k0, k1, v0, v1, (int)n_pad, 0, 32, s));
         const int64_t ntiles = n_pad >> 8;
         int64_t stride = (int64_t)((double)ntiles * 0.6180339887) | 1; // odd, near the golden section of the tile count
         auto gcd = [](int64_t a, int64_t b) { while (b) { const int64_t t = a % b; a = b; b = t; } return a; };
@@ -296,13 +311,9 @@ int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s) {
                                                                           h->norms_s, h->perm);
         tm_count_launch(2);
         TM_CUDA(cudaGetLastError());
-        tm_dev_free(tmp); tm_dev_free(k1); tm_dev_free(v0); tm_dev_free(v1);
     }
-    h->tmap_rows = malloc(3 * sizeof(CUtensorMap)); // [0] rows_f16, [1] norm tiles, [2] rows_f16s (k = 1 scan order)
-    int r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows), r16, n_pad, kp);
-    if (!r) r = make_tmap_norm(static_cast<CUtensorMap *>(h->tmap_rows) + 1, h->norm_tiles, n_pad / 128);
-    if (!r) r = make_tmap(static_cast<CUtensorMap *>(h->tmap_rows) + 2, h->rows_f16s, n_pad, kp);
-    return r;
+    h->rows_f16 = static_cast<__half *>(r16_b.release());
+    return tm_dataset_tensor_maps(h);
 }
 
 int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, int64_t nq_pad, __half *d_q16,
@@ -321,21 +332,11 @@ int tm_make_query_tmap(void *tmap, const __half *d_q16, int64_t nq_pad, int kp) 
 #include "search_tc2_kernel.inc"
 
 // ------------------------------------------------------------------ host orchestration
-// set by the FrameTiling path around a search whose queries are in coherence order (qorder.cu); API lock held
-static bool g_tc_coherent = false;
-void tm_tc_set_coherent(bool on) { g_tc_coherent = on; }
+// set by the FrameTiling path around a search whose queries are in coherence order (qorder.cu); device lock held
+void tm_tc_set_coherent(bool on) { tm_dev()->tc_coherent = on; }
+#define g_tc (tm_dev()->tc)
 
 namespace {
-struct TcScratch {
-    __half *q16 = nullptr;
-    float *qn16 = nullptr, *qne = nullptr, *qde = nullptr, *cand_s = nullptr, *cand_tau = nullptr;
-    int *cand_i = nullptr, *fb_list = nullptr, *fb_count = nullptr;
-    int *h_count = nullptr; // pinned
-    size_t cap_q = 0, cap_c = 0;
-    int kp = 0;
-    std::mutex mu;
-} g_tc;
-
 int ensure_tc_scratch(int64_t nq_pad, int kp, size_t cand_elems, cudaStream_t s) {
     if ((size_t)nq_pad * kp > g_tc.cap_q * (size_t)(g_tc.kp ? g_tc.kp : 1) || kp != g_tc.kp || (size_t)nq_pad > g_tc.cap_q) {
         cudaStreamSynchronize(s);
@@ -381,7 +382,6 @@ int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **
                                 cudaStream_t s) {
     if (!h->rows_f16 || h->kp != h->dd || nq < 1) return 1; // fused operand rows are unpadded: kp == dd only
     const int64_t nq_pad = ((nq + TC_QTILE - 1) / TC_QTILE) * TC_QTILE;
-    std::lock_guard<std::mutex> lk(g_tc.mu);
     int r = ensure_tc_scratch(nq_pad, h->kp, 0, s);
     if (r) return r;
     if (nq_pad > nq) { // zero operand and norms for the padding queries, as operand_kernel writes them
@@ -400,24 +400,21 @@ int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **
 // One coarse pass + re-rank over a query batch.  Queries the certificate rejects are listed in g_tc.fb_list;
 // their number is returned through *nfb_out (one host round trip).  finest_split: use the largest row split
 // (most candidate lists per query) regardless of the batch size - the second chance for rejected queries.
-// Caller holds g_tc.mu.
 static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s,
                    bool operand_ready, bool finest_split, int *nfb_out, int *nlists_out) {
     const int kc = (k <= 4) ? 8 : 16;
     const int nch = h->kp / 64;
     const int64_t nq_pad = ((nq + TC_QTILE - 1) / TC_QTILE) * TC_QTILE;
     const int qblocks = (int)(nq_pad / TC_QTILE);
-    // CTA-pair kernel (default) walks 256-row tiles and keeps two candidate lists per query and row split
-    // (one per accumulator column half); TM_TC_PAIR=0 selects the single-CTA kernel (128-row tiles).
-    static const bool pair = !(getenv("TM_TC_PAIR") && atoi(getenv("TM_TC_PAIR")) == 0);
-    const int tile_rows = pair ? T2_BN : TC_BN;
-    const int total_tiles = (int)(h->n_pad / tile_rows);
+    // the CTA-pair kernel walks 256-row tiles and keeps two candidate lists per query and row split (one per
+    // accumulator column half)
+    const int total_tiles = (int)(h->n_pad / T2_BN);
     // Row split.  A work item costs its tiles plus a start-up (the candidate tracking of a fresh item hits on
     // almost every group until its threshold has settled: measured 20-35 us = roughly 48 tile times), and the
     // items are dealt round-robin to the resident CTA pairs, so the pass takes rounds x (tiles per item + 48).
     // Few query blocks: split the rows so that every SM has work; many: one item per query block.
-    const int units = pair ? tm_num_sms() / 2 : tm_num_sms();
-    const int max_split = pair ? 8 : 16;
+    const int units = tm_num_sms() / 2;
+    const int max_split = 8;
     int nsplit = 1;
     {
         double best = 1e30;
@@ -436,7 +433,7 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     if (nsplit < 1) nsplit = 1;
     int tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
     nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
-    const int nlists = pair ? 2 * nsplit : nsplit;
+    const int nlists = 2 * nsplit;
     *nlists_out = nlists;
 
     int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)nq_pad * nlists * kc, s);
@@ -454,14 +451,13 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     // 77.2 -> 75.2 ms (C2); 1 024 tiles +4 % (C3); unsorted frame calls: 256 tiles per item 0.301 -> 0.329 ms, 340-512
     // tiles 2.24 -> 2.16 ms; 32-85 tiles per item -8 %.
     static const int nf_env = getenv("TM_TC_NF_MIN") ? atoi(getenv("TM_TC_NF_MIN")) : 0; // tuning knob
-    const int nf_min = nf_env > 0 ? nf_env : (g_tc_coherent ? 192 : 320);
-    const bool normfree = k == 1 && pair && tiles_per_split >= nf_min && h->rows_f16s != nullptr;
+    const int nf_min = nf_env > 0 ? nf_env : (tm_dev()->tc_coherent ? 192 : 320);
+    const bool normfree = k == 1 && tiles_per_split >= nf_min && h->rows_f16s != nullptr;
+    g_coarse_launches.fetch_add(1, std::memory_order_relaxed);
     int tok = tm_prof_begin(2, s);
 #define TC_ARGS qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, g_tc.qde, h->max_norm, h->max_dnorm, k, s
-#define TC_LAUNCH(NCH, KC, K1) (pair ? ((K1) && normfree ? launch_tc2<NCH, KC, K1, K1>(tq, tts, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS) \
-                                                    : launch_tc2<NCH, KC, K1, false>(tq, tt, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS)) \
-             \
-                                     : launch_tc<NCH, KC, K1>(tq, tt, h->norm_tiles, h->norm_scale, TC_ARGS))
+#define TC_LAUNCH(NCH, KC, K1) ((K1) && normfree ? launch_tc2<NCH, KC, K1, K1>(tq, tts, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS) \
+                                                : launch_tc2<NCH, KC, K1, false>(tq, tt, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS))
     if (k == 1) r = nch == 1 ? TC_LAUNCH(1, 8, true) : nch == 2 ? TC_LAUNCH(2, 8, true) : TC_LAUNCH(3, 8, true);
     else if (kc == 8) r = nch == 1 ? TC_LAUNCH(1, 8, false) : nch == 2 ? TC_LAUNCH(2, 8, false) : TC_LAUNCH(3, 8, false);
     else r = nch == 1 ? TC_LAUNCH(1, 16, false) : nch == 2 ? TC_LAUNCH(2, 16, false) : TC_LAUNCH(3, 16, false);
@@ -504,7 +500,6 @@ static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int
                           bool operand_ready) {
     if (!h->rows_f16 || k > 8 || ((uintptr_t)d_q & 15)) // outside the tensor-core path's envelope: exact engine
         return tm_launch_search_simt(h->rows_f32, h->n, h->dd, d_q, nq, k, d_idx, d_err, s);
-    std::lock_guard<std::mutex> lk(g_tc.mu);
     int nfb = 0, nlists0 = 0, nlists1 = 0;
     int r = tc_core(h, d_q, nq, k, d_idx, d_err, s, operand_ready, false, &nfb, &nlists0);
     if (r || nfb == 0) return r;
@@ -514,7 +509,7 @@ static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int
     // overflow).  Second chance on the tensor cores with the finest row split - 16 lists per query instead of
     // 2 - on a compacted copy of those queries; what is still rejected goes to the exact engine.  Worth it when
     // the exact scan of the rejects would cost more than a short tensor-core pass.
-    const int finest = 16; // lists per query at the finest split (both kernels)
+    const int finest = 16; // lists per query at the finest split
     const bool retry = (h->dd & 3) == 0 && nfb >= 64 && (double)nfb * (double)h->n >= 2.5e8 && nlists0 < finest &&
                        h->n_pad / 256 >= 32;
     if (!retry) {

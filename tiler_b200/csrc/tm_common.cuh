@@ -6,10 +6,12 @@
 #include <stdio.h>
 #include <atomic>
 #include <mutex>
+#include <vector>
 #include "../../include/tmann.h"
 
 #define TM_DCT 192
 #define TM_KM_FEATURES 80
+#define TM_MAX_DEV 16
 
 // Dataset handle behind the opaque ANNkdtree*.  Layout in HBM:
 //   rows_f32 [n][dd]      float32, exact copy of what crossed the FFI (re-rank / SIMT path)
@@ -50,6 +52,16 @@ struct ANNkdtree {
     // keyframe (stage-2) datasets built by tm_keyframe_dataset_create: row -> (tile, pal, attrs) side tables
     int32_t *h_tr_tile, *h_tr_pal;
     uint8_t *h_tr_attrs;
+    // stage-1 datasets over a tile list with inactive entries (tm_global_dataset_create_active): stage-1 row / 4 ->
+    // index into the caller's tile array (TRToTileIdx main.pas:3763-3777); NULL = every tile is active
+    int32_t *d_tr_tile;
+    int64_t ntiles_all; // length of the caller's tile array (stage-1 datasets)
+    // multi-device (tm_set_devices): rep[0] = this handle on the first active device, rep[i] = its replica on the
+    // i-th; replicas are filled by one NCCL broadcast when the dataset is created.  owner = NULL on the primary.
+    ANNkdtree *rep[TM_MAX_DEV];
+    int nrep;
+    ANNkdtree *owner;
+    std::atomic<unsigned> *rr; // round-robin cursor for calls that go to one replica
 };
 #define TM_MAGIC 0x544d414eu
 
@@ -61,14 +73,72 @@ int tm_check(cudaError_t e, const char *what);
         if (_r) return _r;                          \
     } while (0)
 
-extern std::atomic<int64_t> g_launches, g_queries, g_fallbacks;
+extern std::atomic<int64_t> g_launches, g_queries, g_fallbacks, g_coarse_launches;
 extern int g_engine;
 static inline void tm_count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
-int tm_ensure_device();
-// Stream-ordered device memory from the driver's pool (cudaMallocAsync on the library stream, release threshold
-// unlimited): dataset buffers and per-call temporaries are recycled without cudaMalloc / cudaFree round trips
-// (cudaFree also synchronises the device).  Only for memory used on the library stream.
+// ---- per-device context -------------------------------------------------------------------------------------
+// One per CUDA device the library drives (tm_set_devices; default: the calling thread's current device).  All
+// device work of one GPU goes through its stream and its grow-only scratch under its lock, so callers on
+// different GPUs never wait for each other.  An entry point binds the calling thread to a device for the
+// duration of the call (TmApiGuard in api.cu); everything below the C ABI reaches the context through tm_dev().
+struct TmProfSpan { int tag; cudaEvent_t a, b; };
+struct TmQScratch { // descriptor rows of a query batch (fused FrameTiling path) + coherence-order buffers (qorder.cu)
+    float *desc = nullptr;
+    size_t cap = 0;
+    uint32_t *keys = nullptr;
+    int *vals = nullptr, *perm = nullptr, *inv = nullptr, *idx_s = nullptr;
+    float *err_s = nullptr;
+    void *sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0, cap_order = 0;
+};
+struct TmHostPath { // staging of the host-buffer entry points: two input slots, result buffers, a copy stream
+    void *in[2] = {nullptr, nullptr};
+    int *oi = nullptr;
+    float *oe = nullptr;
+    size_t cap_in = 0, cap_out = 0; // bytes per input slot, result elements
+    cudaStream_t cs = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+};
+struct TmTcScratch { // tensor-core engine: query operand, norms, candidate lists, reject list
+    __half *q16 = nullptr;
+    float *qn16 = nullptr, *qne = nullptr, *qde = nullptr, *cand_s = nullptr, *cand_tau = nullptr;
+    int *cand_i = nullptr, *fb_list = nullptr, *fb_count = nullptr;
+    int *h_count = nullptr; // pinned
+    size_t cap_q = 0, cap_c = 0;
+    int kp = 0;
+};
+struct TmSimtScratch { float *d = nullptr; int *i = nullptr; size_t cap = 0; };
+struct TmDevice {
+    int device = -1, sms = 0;
+    cudaStream_t stream = nullptr, own_stream = nullptr;
+    bool user_stream = false;
+    std::recursive_mutex mu; // serialises this device's entry points (recursive: entry points call each other)
+    TmQScratch qs;
+    TmHostPath hp;
+    TmTcScratch tc;
+    TmSimtScratch simt;
+    bool tc_coherent = false; // the next searches' queries are in coherence order (qorder.cu)
+    std::mutex stats_mu;
+    std::vector<TmProfSpan> spans;
+    float ms[4] = {0, 0, 0, 0};
+    unsigned long long *audit = nullptr; // device: [0] max error ratio (float bits), [1] audited candidates
+    std::atomic<int> inflight{0};        // host calls routed to this device and not yet returned
+    void *nccl_comm = nullptr;           // ncclComm_t of this device in the library's communicator (>= 2 devices)
+};
+TmDevice *tm_dev(); // the calling thread's device context (bound by the entry point)
+static inline cudaStream_t tm_stream() { return tm_dev()->stream; }
+static inline int tm_num_sms() { return tm_dev()->sms; }
+// true the first time it is called for `mask` on the calling thread's device (per-device one-time setup such as
+// cudaFuncSetAttribute, which applies to the current device only); callers hold the device lock
+static inline bool tm_first_on_device(std::atomic<uint32_t> &mask) {
+    const uint32_t bit = 1u << tm_dev()->device;
+    return !(mask.fetch_or(bit, std::memory_order_relaxed) & bit);
+}
+
+// Stream-ordered device memory from the driver's pool (cudaMallocAsync on the device's library stream, release
+// threshold unlimited): dataset buffers and per-call temporaries are recycled without cudaMalloc / cudaFree round
+// trips (cudaFree also synchronises the device).  Only for memory used on that stream.
 cudaError_t tm_dev_malloc_raw(void **p, size_t bytes);
 template <class T> inline cudaError_t tm_dev_malloc(T **p, size_t bytes) {
     return tm_dev_malloc_raw(reinterpret_cast<void **>(p), bytes);
@@ -78,8 +148,6 @@ int tm_prof_begin(int tag, cudaStream_t s); // returns a token (-1 when profilin
 // error-model audit (profiling only): device slots {max ratio as float bits, candidate count}, or nullptr
 unsigned long long *tm_audit_slots();
 void tm_prof_end(int token, cudaStream_t s);
-cudaStream_t tm_stream();
-int tm_num_sms();
 
 // ---- descriptor kernels (psyv.cu)
 int tm_launch_psyv_queries(const int32_t *d_rgb, int64_t nq, int flags, int gamma, float *d_out,
@@ -94,16 +162,19 @@ int tm_launch_psyv_tileset_rows(const uint8_t *d_palpix, int64_t ntiles, const i
                                 const int64_t *d_row_map, int64_t nrows, float *d_out, cudaStream_t s);
 
 // ---- keyframe preparation (keyframe.cu): PrepareFrameTiling main.pas:3791-3967 on the device
+int tm_launch_kf_lines(const uint8_t *d_palpix, int64_t ntiles, float *d_lines, cudaStream_t s);
+// d_tr_tile: stage-1 row / 4 -> tile index (NULL = identity, every tile Active)
 int tm_launch_kf_mark(const int32_t *d_item_pal, const int32_t *d_item_tile, int64_t nitems, int64_t ntiles, int npal,
-                      const int *d_knn_idx, const float *d_knn_err, const uint8_t *d_palmask, uint32_t *d_seen,
-                      uint8_t *d_used, int *d_bad, cudaStream_t s);
+                      const int *d_knn_idx, const float *d_knn_err, const int32_t *d_tr_tile, const uint8_t *d_palmask,
+                      uint32_t *d_seen, uint8_t *d_used, int *d_bad, cudaStream_t s);
 // stream compaction of used[] in index order; *h_count = KNNSize (synchronises s)
 int tm_kf_compact(const uint8_t *d_used, int64_t n, int64_t **d_row_map_out, int64_t *h_count, cudaStream_t s);
 int tm_launch_kf_tables(const int64_t *d_row_map, int64_t nrows, int64_t ntiles, int32_t *d_tr_tile, int32_t *d_tr_pal,
                         uint8_t *d_tr_attrs, cudaStream_t s);
 
-// ---- dataset preparation (prep.cu): mean, centred fp16 operand, norms
+// ---- dataset preparation (search_tc.cu): mean, centred fp16 operand, norms, scan-order copy, TMA descriptors
 int tm_prepare_dataset(ANNkdtree *h, cudaStream_t s);
+int tm_dataset_tensor_maps(ANNkdtree *h);
 // ---- exact SIMT search (search_simt.cu): sequential fp32 accumulation, lowest index on ties
 int tm_launch_search_simt(const float *d_rows, int64_t n, int dd, const float *d_q, int64_t nq, int k,
                           int *d_idx, float *d_err, cudaStream_t s);
