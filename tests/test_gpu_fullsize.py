@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 def env():
     import torch
     import tiler_b200 as tb
-    from bench import synth_queries, synth_tileset
+    from bench import synth_queries, synth_tileset  # the reference LCG (checked against oracle/gen.c on the CPU)
     tb.set_device(0)
     dev = torch.device("cuda", 0)
     gen = torch.Generator(device=dev).manual_seed(1234)

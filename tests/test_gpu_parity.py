@@ -150,7 +150,7 @@ def test_concurrent_callers_share_handles(tb, oracle, small_case):
             for rep in range(6):
                 kind = (w + rep) % 4
                 if kind == 0:
-                    for i in range(w, 64, 8):
+                    for i in range(w % 8, 64, 8):
                         assert t.search(q[i]) == want_single[i]
                 elif kind == 1:
                     gi, ge = t.search_batch(q, 4)
@@ -166,7 +166,7 @@ def test_concurrent_callers_share_handles(tb, oracle, small_case):
         except BaseException as e:  # noqa: BLE001 - reported in the main thread
             errors.append((w, repr(e)))
 
-    threads = [threading.Thread(target=worker, args=(w,)) for w in range(8)]
+    threads = [threading.Thread(target=worker, args=(w,)) for w in range(16)]
     for th in threads:
         th.start()
     for th in threads:
@@ -174,6 +174,29 @@ def test_concurrent_callers_share_handles(tb, oracle, small_case):
     assert not errors, errors[:3]
     t.destroy()
     ft.destroy()
+
+
+def test_frame_calls_with_rejected_queries(tb, oracle, small_case):
+    """Frame-sized host calls are pipelined by the device's worker (api_combine.inc): the tensor-core engine's rejected
+    queries are handled after the batch.  100 copies of one tile put 400 rows at the same distance from their queries -
+    more than a candidate list holds - so those queries are rejected and recomputed on the exact engine; 70 000
+    queries per call also take the coherence order (reject positions translated back).  Result: the exact engine's."""
+    o = oracle
+    tiles = np.concatenate([small_case["tiles"], np.repeat(small_case["tiles"][7:8], 100, 0)])
+    pal = small_case["pal"]
+    rgb_a, s = o.gen_queries(o.BASE_SEED + 5, 35000, tiles[7:8], pal)      # all near the repeated tile (or pure random)
+    rgb_b, s = o.gen_queries(s, 35000, tiles, pal)
+    rgb = np.concatenate([rgb_a, rgb_b])[np.random.default_rng(1).permutation(70000)]
+    with tb.KDTree.from_tileset(tiles, pal) as t:
+        tb.set_engine(tb.ENGINE_SIMT)
+        want = t.frametiling_search(rgb)
+        tb.set_engine(tb.ENGINE_AUTO)
+        for n in (3000, 70000):
+            tb.reset_stats()
+            gi, ge = t.frametiling_search(rgb[:n])
+            st = tb.stats()
+            assert st["coarse_launches"] > 0 and st["fallback_queries"] > n // 8, st
+            assert np.array_equal(gi, want[0][:n]) and np.array_equal(ge.view(np.uint32), want[1][:n].view(np.uint32))
 
 
 def test_search_edge_cases(tb, oracle):

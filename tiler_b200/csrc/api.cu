@@ -632,12 +632,22 @@ int ann_kdtree_search_batch(ANNkdtree *akd, const float *h_q, int64_t nq, int k,
     return search_batch_one(pick_replica(akd, nullptr), h_q, nq, k, h_idxs, h_errs);
 }
 
-// legacy single-query entry points: re-entrant (per-handle mutex around the pinned scratch)
+namespace {
+bool combine_on();
+int search_one_combined(ANNkdtree *akd, const float *q, int k, int *idxs, float *errs);
+} // namespace
+
+// legacy single-query entry points: re-entrant.  Concurrent callers are coalesced into one device batch by the
+// device's worker (api_combine.inc); TM_COMBINE=0 serves them one by one under the device lock.
 static int search_one(ANNkdtree *akd, const float *q, int k, int *idxs, float *errs) {
     if (valid(akd)) return -1;
     if (k < 1 || k > 16 || !q) return -1;
     akd = pick_replica(akd, nullptr);
     InflightMark mark(akd);
+    if (combine_on() && akd->dd <= 256) {
+        if (!tm_primary()) return -1;
+        return search_one_combined(akd, q, k, idxs, errs);
+    }
     TM_API_GUARD_H(akd);
     if (tm_ensure_device()) return -1;
     std::lock_guard<std::mutex> lk(*akd->single_mu);
@@ -748,4 +758,5 @@ int tm_set_profiling(int on) {
 } // extern "C"
 
 #include "api_fused.inc"
+#include "api_combine.inc"
 #include "api_keyframe.inc"

@@ -102,6 +102,20 @@ int tm_launch_query_order(const int32_t *d_rgb, int64_t nq, uint32_t *d_keys /* 
     return tm_check(cudaGetLastError(), "invert_order_kernel");
 }
 
+// deferred reject list of a batch searched in coherence order: sorted position -> position in the caller's order
+__global__ void translate_list_kernel(int *__restrict__ list, const int *__restrict__ count, int64_t cap,
+                                      const int *__restrict__ perm) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < cap && i < *count) list[i] = perm[list[i]];
+}
+
+int tm_launch_translate_list(int *d_list, const int *d_count, int64_t cap, const int *d_perm, cudaStream_t s) {
+    if (cap <= 0) return 0;
+    translate_list_kernel<<<(unsigned)((cap + 255) / 256), 256, 0, s>>>(d_list, d_count, cap, d_perm);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "translate_list_kernel");
+}
+
 int tm_launch_scatter_query_results(const int *d_perm, int64_t nq, const int *d_idx_s, const float *d_err_s, int *d_idx,
                                     float *d_err, cudaStream_t s) {
     if (nq == 0) return 0;

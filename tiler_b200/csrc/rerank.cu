@@ -170,7 +170,9 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
         }
     // certificate: no row outside the candidate lists can be at or below the k-th exact distance.
     // NaN / overflowed fp16 query operands never certify (their scores are NaN and select nothing).
-    bool ok = !overflow && qn16[qg] < 3.0e38f;
+    // A k-th distance must exist: with no candidate at all (dk = inf) there is nothing the bound could be compared
+    // with - the exact engine answers (it also serves datasets with fewer than k rows).
+    bool ok = !overflow && qn16[qg] < 3.0e38f && dk < INFINITY;
     if (ok && tau < INFINITY) {
         const float nsumf = qne[qg] + max_tnorm;
         const double nsum = (double)nsumf;

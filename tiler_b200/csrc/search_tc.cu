@@ -470,6 +470,15 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
                          g_tc.qde, h->max_norm, h->max_dnorm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
     tm_prof_end(tok, s);
     if (r) return r;
+    if (TmDefer *df = tm_dev()->defer) {
+        // pipelined caller (api_combine.inc): no host round trip here; the reject count and list travel with the
+        // results and are handled after the batch has completed
+        const int64_t nl = std::min<int64_t>(nq, df->cap);
+        TM_CUDA(cudaMemcpyAsync(df->h_count, g_tc.fb_count, sizeof(int), cudaMemcpyDeviceToHost, s));
+        TM_CUDA(cudaMemcpyAsync(df->d_list, g_tc.fb_list, sizeof(int) * (size_t)nl, cudaMemcpyDeviceToDevice, s));
+        *nfb_out = 0;
+        return 0;
+    }
     TM_CUDA(cudaMemcpyAsync(g_tc.h_count, g_tc.fb_count, sizeof(int), cudaMemcpyDeviceToHost, s));
     TM_CUDA(cudaStreamSynchronize(s));
     *nfb_out = *g_tc.h_count;
@@ -495,6 +504,22 @@ __global__ void scatter_results_kernel(const int *__restrict__ list, int n, int 
     err[(int64_t)list[i] * k + j] = te[e];
 }
 } // namespace
+
+int tm_launch_gather_rows(const float *d_rows, const int *d_list, int n, int dd, float *d_out, cudaStream_t s) {
+    if (n == 0) return 0;
+    const int64_t total = (int64_t)n * (dd >> 2);
+    gather_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(d_rows, d_list, n, dd, d_out);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "gather_rows_kernel");
+}
+
+int tm_launch_scatter_results(const int *d_list, int n, int k, const int *d_ti, const float *d_te, int *d_idx, float *d_err,
+                              cudaStream_t s) {
+    if (n == 0) return 0;
+    scatter_results_kernel<<<(unsigned)(((int64_t)n * k + 255) / 256), 256, 0, s>>>(d_list, n, k, d_ti, d_te, d_idx, d_err);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "scatter_results_kernel");
+}
 
 static int search_tc_impl(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s,
                           bool operand_ready) {

@@ -108,6 +108,9 @@ struct TmTcScratch { // tensor-core engine: query operand, norms, candidate list
     size_t cap_q = 0, cap_c = 0;
     int kp = 0;
 };
+// deferred handling of the queries the tensor-core certificate rejects (pipelined host calls, api_combine.inc)
+struct TmDefer { int *d_list; int *h_count; int64_t cap; };
+struct TmCombiner; // api_combine.inc: per-device worker that coalesces concurrent frame-sized / single-query host calls
 struct TmSimtScratch { float *d = nullptr; int *i = nullptr; size_t cap = 0; };
 struct TmDevice {
     int device = -1, sms = 0;
@@ -119,6 +122,8 @@ struct TmDevice {
     TmTcScratch tc;
     TmSimtScratch simt;
     bool tc_coherent = false; // the next searches' queries are in coherence order (qorder.cu)
+    TmDefer *defer = nullptr; // set around a search whose rejected queries the caller handles after completion
+    std::atomic<TmCombiner *> combiner{nullptr};
     std::mutex stats_mu;
     std::vector<TmProfSpan> spans;
     float ms[4] = {0, 0, 0, 0};
@@ -202,6 +207,7 @@ int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, 
 size_t tm_query_order_temp_bytes(int64_t nq);
 int tm_launch_query_order(const int32_t *d_rgb, int64_t nq, uint32_t *d_keys /* [2][nq] */, int *d_vals /* [nq] */,
                           int *d_perm, int *d_inv, void *d_tmp, size_t tmp_bytes, cudaStream_t s);
+int tm_launch_translate_list(int *d_list, const int *d_count, int64_t cap, const int *d_perm, cudaStream_t s);
 int tm_launch_scatter_query_results(const int *d_perm, int64_t nq, const int *d_idx_s, const float *d_err_s, int *d_idx,
                                     float *d_err, cudaStream_t s);
 // tensor-core engine with a query operand supplied by the caller: tm_tc_query_operand_buffers hands out the engine's
@@ -210,6 +216,10 @@ int tm_tc_query_operand_buffers(ANNkdtree *h, int64_t nq, void **d_q16, float **
                                 cudaStream_t s);
 void tm_tc_set_coherent(bool on); // hint: the next searches' queries are in coherence order (qorder.cu)
 int tm_search_tc_prepared(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, float *d_err, cudaStream_t s);
+// rows of dd floats (dd % 4 == 0) gathered by index list / (idx, err)[n][k] scattered back by the same list
+int tm_launch_gather_rows(const float *d_rows, const int *d_list, int n, int dd, float *d_out, cudaStream_t s);
+int tm_launch_scatter_results(const int *d_list, int n, int k, const int *d_ti, const float *d_te, int *d_idx, float *d_err,
+                              cudaStream_t s);
 int tm_launch_temporal_smoothing(const uint8_t *d_palpix, int64_t ntiles, const int32_t *d_pals, int npal, int pal_size,
                                  const int32_t *d_frame_kf, int64_t nframes, int64_t npos, const int32_t *d_tile,
                                  const int32_t *d_pal, const uint8_t *d_attrs, double strength, int32_t *d_src_frame,
