@@ -634,6 +634,7 @@ int ann_kdtree_search_batch(ANNkdtree *akd, const float *h_q, int64_t nq, int k,
 
 namespace {
 bool combine_on();
+bool combiner_idle(TmDevice *d);
 int search_one_combined(ANNkdtree *akd, const float *q, int k, int *idxs, float *errs);
 } // namespace
 
@@ -644,9 +645,10 @@ static int search_one(ANNkdtree *akd, const float *q, int k, int *idxs, float *e
     if (k < 1 || k > 16 || !q) return -1;
     akd = pick_replica(akd, nullptr);
     InflightMark mark(akd);
-    if (combine_on() && akd->dd <= 256) {
-        if (!tm_primary()) return -1;
-        return search_one_combined(akd, q, k, idxs, errs);
+    {
+        TmDevice *dv = g_ctx[akd->device];
+        const bool contended = dv->inflight.load(std::memory_order_relaxed) > 1 || !combiner_idle(dv);
+        if (combine_on() && akd->dd <= 256 && contended) return search_one_combined(akd, q, k, idxs, errs);
     }
     TM_API_GUARD_H(akd);
     if (tm_ensure_device()) return -1;

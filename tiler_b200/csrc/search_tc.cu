@@ -339,6 +339,9 @@ void tm_tc_set_coherent(bool on) { tm_dev()->tc_coherent = on; }
 namespace {
 int ensure_tc_scratch(int64_t nq_pad, int kp, size_t cand_elems, cudaStream_t s) {
     if ((size_t)nq_pad * kp > g_tc.cap_q * (size_t)(g_tc.kp ? g_tc.kp : 1) || kp != g_tc.kp || (size_t)nq_pad > g_tc.cap_q) {
+        // grow-only, geometric (every step costs a synchronisation and five cudaMallocs), whole query tiles
+        if (kp == g_tc.kp && (size_t)nq_pad < g_tc.cap_q + g_tc.cap_q / 2)
+            nq_pad = (int64_t)(((g_tc.cap_q + g_tc.cap_q / 2 + TC_QTILE - 1) / TC_QTILE) * TC_QTILE);
         cudaStreamSynchronize(s);
         cudaFree(g_tc.q16); cudaFree(g_tc.qn16); cudaFree(g_tc.qne); cudaFree(g_tc.qde); cudaFree(g_tc.fb_list);
         g_tc.q16 = nullptr; g_tc.cap_q = 0;
@@ -351,6 +354,7 @@ int ensure_tc_scratch(int64_t nq_pad, int kp, size_t cand_elems, cudaStream_t s)
         g_tc.kp = kp;
     }
     if (cand_elems > g_tc.cap_c) {
+        if (cand_elems < g_tc.cap_c + g_tc.cap_c / 2) cand_elems = g_tc.cap_c + g_tc.cap_c / 2;
         cudaStreamSynchronize(s);
         cudaFree(g_tc.cand_s); cudaFree(g_tc.cand_i); cudaFree(g_tc.cand_tau);
         g_tc.cand_s = nullptr; g_tc.cap_c = 0;
