@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtmann.so")
+# TMANN_LIB: an alternative build of the same library (the debug-sweep build of scripts/dbg_sweep.sh), never a fallback
+LIB_PATH = os.environ.get("TMANN_LIB") or os.path.join(_HERE, "libtmann.so")
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

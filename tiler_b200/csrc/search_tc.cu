@@ -474,6 +474,12 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
                          g_tc.qde, h->max_norm, h->max_dnorm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
     tm_prof_end(tok, s);
     if (r) return r;
+#ifdef TM_DEBUG_SWEEP
+    if (tc_debug_mode()) { // the sweep modes skip candidate tracking: results are garbage, do not send them to the exact engine
+        *nfb_out = 0;
+        return 0;
+    }
+#endif
     if (TmDefer *df = tm_dev()->defer) {
         // pipelined caller (api_combine.inc): no host round trip here; the reject count and list travel with the
         // results and are handled after the batch has completed
