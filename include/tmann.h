@@ -201,6 +201,21 @@ TM_API int tm_kmodes_assign(const uint8_t *h_X, int64_t npoints, const uint8_t *
                             int64_t k, int semantics, int32_t *h_clust, uint64_t *h_dis);
 TM_API int tm_kmodes_assign_dev(const uint8_t *d_X, int64_t npoints, const uint8_t *d_centroids,
                                 int64_t k, int semantics, int32_t *d_clust, uint64_t *d_dis);
+/* Device-resident KModes state for the per-bin loop of KModesIter (kmodes.pas:845-909): the points are
+ * uploaded once, the centroids stay on the device, the caller sends only the rows MovePointCat changed
+ * (kmodes.pas:778-806) between two 960-point bins and gets one bin's (clust, dis) per call.  Same kernel,
+ * same results as tm_kmodes_assign; no allocation and one synchronisation per bin. */
+typedef struct tm_kmodes tm_kmodes;
+TM_API tm_kmodes *tm_kmodes_open(const uint8_t *h_X, int64_t npoints, int semantics);
+TM_API void tm_kmodes_close(tm_kmodes *km);
+/* all k centroids [k][80] (after InitFarthestFirst / the initial mode computation, kmodes.pas:999-1016) */
+TM_API int tm_kmodes_set_centroids(tm_kmodes *km, const uint8_t *h_centroids, int64_t k);
+/* h_rows[m][80] replace the centroids h_idx[m] (duplicates: the last one wins like sequential stores) */
+TM_API int tm_kmodes_update_centroids(tm_kmodes *km, const int32_t *h_idx, const uint8_t *h_rows, int64_t m);
+/* DoGMMD for the points [lo, hi): h_clust[hi-lo], h_dis[hi-lo] (may be NULL) */
+TM_API int tm_kmodes_assign_range(tm_kmodes *km, int64_t lo, int64_t hi, int32_t *h_clust, uint64_t *h_dis);
+TM_API int tm_kmodes_read_centroids(tm_kmodes *km, uint8_t *h_centroids);
+
 /* UpdateMinDistance (kmodes.pas:455-596): mindist[i] = min(mindist[i], dissim(center, X[i])) */
 TM_API int tm_kmodes_update_min_distance(const uint8_t *h_X, int64_t npoints,
                                          const uint8_t *h_center, int semantics,

@@ -112,6 +112,9 @@ void tmo_farthest_first(const uint8_t *X, int64_t npoints, int64_t k, int64_t in
 /* representative pick of DoKModes main.pas:4231-4253 */
 void tmo_kmodes_representatives(const uint8_t *X, int64_t npoints, const int32_t *labels,
                                 const uint8_t *centroids, int64_t k, int semantics, int32_t *rep, int32_t *count);
+/* ComputeKModes kmodes.pas:917-1060 (ANumInit <= 0: one run from start_point) incl. KModesIter 845-909 */
+int tmo_compute_kmodes(const uint8_t *X, int64_t npoints, int64_t k, int64_t start_point, int nmod, int semantics,
+                       int max_iter, int32_t *labels, uint8_t *centroids, uint64_t *cost_out, int64_t *moves_out);
 /* WriteTileDatasetLine main.pas:4167-4183 + GetTilePalZoneThres 4142-4165 */
 int  tmo_kmodes_row(const uint8_t *palpix, int pal_size, uint8_t *row80);
 

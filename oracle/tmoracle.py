@@ -296,6 +296,18 @@ def kmodes_representatives(X, labels, centroids, semantics=ASM):
     return rep, cnt
 
 
+def compute_kmodes(X, k, start_point, nmod=16, semantics=ASM, max_iter=0):
+    """TKModes.ComputeKModes (kmodes.pas:917-1060, one run from start_point).  Returns (labels, centroids, n_iter, cost, moves)."""
+    X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+    labels = np.empty(X.shape[0], np.int32)
+    cent = np.empty((k, 80), np.uint8)
+    cost = C.c_uint64()
+    moves = C.c_int64()
+    it = _lib.tmo_compute_kmodes(_p(X, C.c_uint8), i64(X.shape[0]), i64(k), i64(start_point), int(nmod), int(semantics),
+                                 int(max_iter), _p(labels, C.c_int32), _p(cent, C.c_uint8), C.byref(cost), C.byref(moves))
+    return labels, cent, int(it), int(cost.value), int(moves.value)
+
+
 def kmodes_row(palpix, pal_size=16):
     palpix = np.ascontiguousarray(palpix, np.uint8).reshape(64)
     row = np.empty(80, np.uint8)

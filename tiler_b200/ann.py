@@ -257,6 +257,51 @@ def kmodes_assign(X, centroids, semantics=KM_ASM, out_clust=None, out_dis=None):
     return clust, dis
 
 
+class KModesState:
+    """Device-resident points + centroids for the per-bin loop of KModesIter (kmodes.pas:845-909)."""
+
+    def __init__(self, X, semantics=KM_ASM):
+        self._h = None
+        X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
+        self.n = X.shape[0]
+        self.k = 0
+        self._h = check_handle(lib.tm_kmodes_open(_hp(X), self.n, int(semantics)))
+
+    def set_centroids(self, centroids):
+        centroids = np.ascontiguousarray(centroids, np.uint8).reshape(-1, 80)
+        check(lib.tm_kmodes_set_centroids(self._h, _hp(centroids), centroids.shape[0]))
+        self.k = centroids.shape[0]
+
+    def update_centroids(self, idx, rows):
+        idx = np.ascontiguousarray(idx, np.int32)
+        rows = np.ascontiguousarray(rows, np.uint8).reshape(-1, 80)
+        check(lib.tm_kmodes_update_centroids(self._h, _hp(idx), _hp(rows), len(idx)))
+
+    def assign_range(self, lo, hi, with_dis=True):
+        clust = np.empty(hi - lo, np.int32)
+        dis = np.empty(hi - lo, np.uint64) if with_dis else None
+        check(lib.tm_kmodes_assign_range(self._h, int(lo), int(hi), _hp(clust), _hp(dis)))
+        return clust, dis
+
+    def centroids(self):
+        out = np.empty((self.k, 80), np.uint8)
+        check(lib.tm_kmodes_read_centroids(self._h, _hp(out)))
+        return out
+
+    def close(self):
+        if self._h:
+            lib.tm_kmodes_close(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
 def kmodes_update_min_distance(X, center, mindist, semantics=KM_ASM):
     X = np.ascontiguousarray(X, np.uint8).reshape(-1, 80)
     center = np.ascontiguousarray(center, np.uint8)

@@ -762,3 +762,4 @@ int tm_set_profiling(int on) {
 #include "api_fused.inc"
 #include "api_combine.inc"
 #include "api_keyframe.inc"
+#include "api_kmodes.inc"

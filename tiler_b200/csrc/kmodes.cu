@@ -127,6 +127,29 @@ __global__ void kmodes_pack_centroids_kernel(const uint32_t *__restrict__ C, int
     dst[2] = make_uint4(o[8], o[9], o[10], o[11]);
 }
 
+// KModes handle (tm_kmodes_update_centroids): rows[m][80] replace the centroids idx[m] - byte rows and bit-sliced
+// copies in one pass (MovePointCat changes a handful of centroids between two 960-point bins, kmodes.pas:880-909)
+__global__ void kmodes_update_centroids_kernel(const uint32_t *__restrict__ rows, const int32_t *__restrict__ idx, int64_t m,
+                                               int64_t k, uint32_t *__restrict__ C, uint32_t *__restrict__ Cb,
+                                               int *__restrict__ wide_flag, int *__restrict__ bad) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const int64_t c = idx[i];
+    if (c < 0 || c >= k) { atomicOr(bad, 1); return; }
+    uint32_t p[KM_WORDS], wide = 0;
+#pragma unroll
+    for (int w = 0; w < KM_WORDS; w++) {
+        p[w] = rows[i * KM_WORDS + w];
+        C[c * KM_WORDS + w] = p[w];
+        wide |= p[w];
+    }
+    if (wide & 0xf0f0f0f0u) atomicOr(wide_flag, 1);
+    uint32_t o[KM_BWORDS];
+    bitslice_row(p, o);
+#pragma unroll
+    for (int w = 0; w < KM_BWORDS; w++) Cb[c * KM_BWORDS + w] = o[w];
+}
+
 template <int SEM>
 __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *__restrict__ X, int64_t np,
                                                              const uint32_t *__restrict__ C, int64_t k,
@@ -381,37 +404,47 @@ __global__ void kmodes_rows_kernel(const uint8_t *__restrict__ palpix, int64_t n
 
 } // namespace
 
-namespace {
-struct KmScratch { // grow-only: bit-sliced centroids + wide flag
-    uint32_t *cb = nullptr;
-    int *flag = nullptr;
-    size_t cap = 0;
-    int32_t *part_i = nullptr; // [parts][points] partial arg-min of the centroid-split launch
-    uint32_t *part_d = nullptr;
-    size_t cap_part = 0;
-    std::mutex mu;
-} g_km;
-} // namespace
+// bit-sliced centroids, the "some byte >= 16" flag and the partial arg-min buffers of a centroid-split launch
+// (TmKmScratch, tm_common.cuh): one set per device for the one-shot entry points, one per KModes handle
+#define g_km (tm_dev()->km)
 
-int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
-                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s) {
-    if (sem != TM_KM_ASM && sem != TM_KM_GENERIC) { tm_set_error("unknown KModes semantics %d", sem); return TM_EINVAL; }
-    if (np == 0) return 0;
-    if (((uintptr_t)d_X & 15) || ((uintptr_t)d_c & 15)) { tm_set_error("KModes rows must be 16-byte aligned"); return TM_EINVAL; }
-    std::lock_guard<std::mutex> lk(g_km.mu);
-    if ((size_t)k > g_km.cap || !g_km.flag) {
+static int km_ensure_centroids(TmKmScratch &c, int64_t k, cudaStream_t s) {
+    if ((size_t)k > c.cap || !c.flag) {
         cudaStreamSynchronize(s);
-        cudaFree(g_km.cb);
-        g_km.cb = nullptr; g_km.cap = 0;
-        TM_CUDA(cudaMalloc(&g_km.cb, sizeof(uint32_t) * KM_BWORDS * (size_t)(k > 0 ? k : 1)));
-        if (!g_km.flag) TM_CUDA(cudaMalloc(&g_km.flag, sizeof(int)));
-        g_km.cap = (size_t)(k > 0 ? k : 1);
+        cudaFree(c.cb);
+        c.cb = nullptr; c.cap = 0;
+        TM_CUDA(cudaMalloc(&c.cb, sizeof(uint32_t) * KM_BWORDS * (size_t)(k > 0 ? k : 1)));
+        if (!c.flag) TM_CUDA(cudaMalloc(&c.flag, sizeof(int)));
+        c.cap = (size_t)(k > 0 ? k : 1);
     }
-    TM_CUDA(cudaMemsetAsync(g_km.flag, 0, sizeof(int), s));
+    return 0;
+}
+
+// bit-sliced copy of all k centroids + wide flag
+int tm_kmodes_pack_centroids(TmKmScratch &c, const uint8_t *d_c, int64_t k, cudaStream_t s) {
+    int r = km_ensure_centroids(c, k, s);
+    if (r) return r;
+    TM_CUDA(cudaMemsetAsync(c.flag, 0, sizeof(int), s));
     if (k > 0) {
-        kmodes_pack_centroids_kernel<<<(unsigned)((k + 127) / 128), 128, 0, s>>>((const uint32_t *)d_c, k, g_km.cb, g_km.flag);
+        kmodes_pack_centroids_kernel<<<(unsigned)((k + 127) / 128), 128, 0, s>>>((const uint32_t *)d_c, k, c.cb, c.flag);
         tm_count_launch();
     }
+    return tm_check(cudaGetLastError(), "kmodes_pack_centroids_kernel");
+}
+
+int tm_kmodes_update_packed(TmKmScratch &c, uint8_t *d_c, int64_t k, const uint8_t *d_rows, const int32_t *d_idx, int64_t m,
+                            int *d_bad, cudaStream_t s) {
+    if (m == 0) return 0;
+    kmodes_update_centroids_kernel<<<(unsigned)((m + 127) / 128), 128, 0, s>>>((const uint32_t *)d_rows, d_idx, m, k, (uint32_t *)d_c,
+                                                                              c.cb, c.flag, d_bad);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "kmodes_update_centroids_kernel");
+}
+
+// assignment of np points against centroids already packed in c
+int tm_kmodes_assign_packed(TmKmScratch &c, const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
+                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s) {
+    if (np == 0) return 0;
     const unsigned gx = (unsigned)((np + 255) / 256);
     // Few points (KModesIter's bins of 960, kmodes.pas:847): thread-per-point alone would occupy a handful of SMs,
     // so the centroids are split over gridDim.y in multiples of the shared-memory tile and merged afterwards.
@@ -425,26 +458,41 @@ int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, 
     if (parts > 1) {
         parts = (int)((k + cchunk - 1) / cchunk);
         const size_t need = (size_t)parts * (size_t)np;
-        if (need > g_km.cap_part) {
+        if (need > c.cap_part) {
             cudaStreamSynchronize(s);
-            cudaFree(g_km.part_i); cudaFree(g_km.part_d);
-            g_km.part_i = nullptr; g_km.part_d = nullptr; g_km.cap_part = 0;
-            TM_CUDA(cudaMalloc(&g_km.part_i, sizeof(int32_t) * need));
-            TM_CUDA(cudaMalloc(&g_km.part_d, sizeof(uint32_t) * need));
-            g_km.cap_part = need;
+            cudaFree(c.part_i); cudaFree(c.part_d);
+            c.part_i = nullptr; c.part_d = nullptr; c.cap_part = 0;
+            TM_CUDA(cudaMalloc(&c.part_i, sizeof(int32_t) * need));
+            TM_CUDA(cudaMalloc(&c.part_d, sizeof(uint32_t) * need));
+            c.cap_part = need;
         }
     }
     const dim3 grid(gx, (unsigned)parts);
     if (sem == TM_KM_ASM)
-        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis, cchunk, g_km.part_i, g_km.part_d);
+        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, d_clust, d_dis, cchunk, c.part_i, c.part_d);
     else
-        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, g_km.cb, g_km.flag, d_clust, d_dis, cchunk, g_km.part_i, g_km.part_d);
+        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, d_clust, d_dis, cchunk, c.part_i, c.part_d);
     if (parts > 1) {
-        kmodes_merge_kernel<<<gx, 256, 0, s>>>(g_km.part_i, g_km.part_d, np, parts, d_clust, d_dis);
+        kmodes_merge_kernel<<<gx, 256, 0, s>>>(c.part_i, c.part_d, np, parts, d_clust, d_dis);
         tm_count_launch();
     }
     tm_count_launch();
     return tm_check(cudaGetLastError(), "kmodes_assign_kernel");
+}
+
+void tm_kmodes_scratch_free(TmKmScratch &c) {
+    cudaFree(c.cb); cudaFree(c.flag); cudaFree(c.part_i); cudaFree(c.part_d);
+    c = TmKmScratch();
+}
+
+int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
+                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s) {
+    if (sem != TM_KM_ASM && sem != TM_KM_GENERIC) { tm_set_error("unknown KModes semantics %d", sem); return TM_EINVAL; }
+    if (np == 0) return 0;
+    if (((uintptr_t)d_X & 15) || ((uintptr_t)d_c & 15)) { tm_set_error("KModes rows must be 16-byte aligned"); return TM_EINVAL; }
+    int r = tm_kmodes_pack_centroids(g_km, d_c, k, s);
+    if (r) return r;
+    return tm_kmodes_assign_packed(g_km, d_X, np, d_c, k, sem, d_clust, d_dis, s);
 }
 
 int tm_launch_kmodes_umd(const uint8_t *d_X, int64_t np, const uint8_t *d_center, int sem, uint64_t *d_mind,

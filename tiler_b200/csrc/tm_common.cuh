@@ -111,6 +111,14 @@ struct TmTcScratch { // tensor-core engine: query operand, norms, candidate list
 // deferred handling of the queries the tensor-core certificate rejects (pipelined host calls, api_combine.inc)
 struct TmDefer { int *d_list; int *h_count; int64_t cap; };
 struct TmCombiner; // api_combine.inc: per-device worker that coalesces concurrent frame-sized / single-query host calls
+struct TmKmScratch { // KModes: bit-sliced centroids + wide flag, partial arg-min of a centroid-split launch (grow-only)
+    uint32_t *cb = nullptr;
+    int *flag = nullptr;
+    size_t cap = 0;
+    int32_t *part_i = nullptr;
+    uint32_t *part_d = nullptr;
+    size_t cap_part = 0;
+};
 struct TmSimtScratch { float *d = nullptr; int *i = nullptr; size_t cap = 0; };
 struct TmDevice {
     int device = -1, sms = 0;
@@ -121,6 +129,7 @@ struct TmDevice {
     TmHostPath hp;
     TmTcScratch tc;
     TmSimtScratch simt;
+    TmKmScratch km;
     bool tc_coherent = false; // the next searches' queries are in coherence order (qorder.cu)
     TmDefer *defer = nullptr; // set around a search whose rejected queries the caller handles after completion
     std::atomic<TmCombiner *> combiner{nullptr};
@@ -193,6 +202,12 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
 // ---- kmodes (kmodes.cu)
 int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
                             int32_t *d_clust, uint64_t *d_dis, cudaStream_t s);
+int tm_kmodes_pack_centroids(TmKmScratch &c, const uint8_t *d_c, int64_t k, cudaStream_t s);
+int tm_kmodes_update_packed(TmKmScratch &c, uint8_t *d_c, int64_t k, const uint8_t *d_rows, const int32_t *d_idx, int64_t m,
+                            int *d_bad, cudaStream_t s);
+int tm_kmodes_assign_packed(TmKmScratch &c, const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
+                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s);
+void tm_kmodes_scratch_free(TmKmScratch &c);
 int tm_launch_kmodes_farthest_first(const uint8_t *d_X, int64_t np, int64_t k, int64_t init_point, int sem,
                                     uint8_t *d_centroids, int64_t *d_chosen, unsigned long long *d_argkey,
                                     uint32_t *d_mind, uint8_t *d_used, int *d_err, cudaStream_t s);
