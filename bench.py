@@ -447,6 +447,28 @@ def helper_kernels(torch, tb, dev, stream, hbm_gbs, reps=3):
                                "byte_compares_per_s": npnt * k * 80 / ms * 1e3, "algorithmic_bytes": b,
                                "achieved_gbs": b / ms / 1e6, "hbm_frac": b / ms / 1e6 / hbm_gbs,
                                "bound": "integer ALU (HBM floor %.0f us)" % (b / hbm_gbs / 1e3)}
+    # one KModesIter over C4 (kmodes.pas:845-909): 1 093 bins of 960 points through the device-resident handle, a few
+    # changed centroid rows sent before every bin (what MovePointCat edits), host wall clock (library time)
+    Xh, Ch = X.cpu().numpy(), cent.cpu().numpy()
+    rng = np.random.default_rng(0)
+    from tiler_b200._lib import lib as _l
+    import ctypes as _C
+    with tb.KModesState(Xh) as stt:
+        stt.set_centroids(Ch)
+        stt.assign_range(0, 960)
+        cl, di = np.empty(960, np.int32), np.empty(960, np.uint64)
+        idx = rng.integers(0, k, (1100, 4)).astype(np.int32)
+        rows = np.ascontiguousarray(Ch[idx])  # [1100][4][80]
+        vp = _C.c_void_p
+        t0 = time.perf_counter()
+        nb = 0
+        for lo in range(0, npnt, 960):  # preallocated buffers, raw C-ABI calls: what a compiled host pays
+            _l.tm_kmodes_update_centroids(stt._h, vp(idx[nb].ctypes.data), vp(rows[nb].ctypes.data), 4)
+            _l.tm_kmodes_assign_range(stt._h, lo, min(npnt, lo + 960), vp(cl.ctypes.data), vp(di.ctypes.data))
+            nb += 1
+        dt = time.perf_counter() - t0
+    out["kmodes_iter_c4_handle"] = {"bins": nb, "ms": 1e3 * dt, "us_per_bin": 1e6 * dt / nb, "pairs_per_s": npnt * k / dt,
+                                    "note": "tm_kmodes_update_centroids (4 rows) + tm_kmodes_assign_range per 960-point bin"}
     return out
 
 
