@@ -69,6 +69,23 @@ def test_tc_every_operand_width(tb, oracle, dd, k):
     assert np.array_equal(te[:64].view(np.uint32), od.view(np.uint32))
 
 
+@pytest.mark.parametrize("nblocks,extra,k", [(75, 0, 1), (80, 5, 1), (100, -3, 1), (149, 1, 8), (81, 0, 4), (223, 17, 1)])
+def test_tc_tail_plan_equals_exact_engine(tb, oracle, nblocks, extra, k):
+    """Query-block counts that leave a few blocks for the last round of the 74 CTA pairs: those blocks are cut into
+    finer row splits (TcPlan, search_tc.h) and carry more candidate lists than the others.  Bit-identical to the exact
+    engine, whichever part of the plan a query falls in."""
+    rng = np.random.default_rng(nblocks * 7 + k)
+    n, nq = 9000, nblocks * 256 + extra
+    ds = rng.standard_normal((n, 192)).astype(np.float32)
+    q = (ds[rng.integers(0, n, nq)] + 0.2 * rng.standard_normal((nq, 192))).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        si, se, ti, te, st = _both(tb, t, q, k)
+    assert st["coarse_launches"] > 0, st
+    assert np.array_equal(si, ti) and np.array_equal(se.view(np.uint32), te.view(np.uint32))
+    oi, od = oracle.knn_f32(ds, q[-64:], k)           # the tail blocks against the oracle
+    assert np.array_equal(te[-64:].view(np.uint32), od.view(np.uint32))
+
+
 def test_tc_envelope_is_visible_in_the_counters(tb):
     """k > 8 and datasets wider than 192 are outside the tensor-core path: the exact engine answers, and the
     launch counter says so (no silent substitution inside a 'tensor-core' test)."""

@@ -49,7 +49,7 @@ constexpr int RR_SEG_STRIDE = 36;     // floats per staged row segment (pad: con
 template <bool K1, bool STAGED>
 __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     const float *__restrict__ rows, int dd, const float *__restrict__ q, int64_t nq,
-    const float *__restrict__ cand_s, const int *__restrict__ cand_i, const float *__restrict__ cand_tau, int nlists, int kc,
+    const float *__restrict__ cand_s, const int *__restrict__ cand_i, const float *__restrict__ cand_tau, const TcPlan plan, int kc,
     const float *__restrict__ qn16, const float *__restrict__ qne, const float *__restrict__ qde, float max_tnorm,
     float max_dnorm, int k, int maxv,
     int *__restrict__ idx, float *__restrict__ err, int *__restrict__ fb_list, int *__restrict__ fb_count,
@@ -61,6 +61,9 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     const int64_t qg = (int64_t)blockIdx.x * RR_THREADS + threadIdx.x;
     const bool live = qg < nq;
     const int64_t qc = live ? qg : nq - 1; // clamped: dead lanes still help with the cooperative loads
+    // this query's candidate lists (search_tc.h: a query of the plan's tail has more, shorter-range lists)
+    const int nlists = plan.nlists(qc);
+    const int64_t lbase = plan.list_base(qc);
     const int C = nlists * kc;
     // Rows scored at or above the final admission threshold are covered by the certificate's lower bound
     // exactly like rows that were never admitted: only the ones below it need exact distances.
@@ -68,9 +71,9 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     int cnt = 0;
     bool overflow = false;
     if (live) {
-        for (int l = 0; l < nlists; l++) tau = fminf(tau, cand_tau[qg * nlists + l]);
-        const int4 *ci4 = reinterpret_cast<const int4 *>(cand_i + qg * C);
-        const float4 *cs4 = reinterpret_cast<const float4 *>(cand_s + qg * C);
+        for (int l = 0; l < nlists; l++) tau = fminf(tau, cand_tau[lbase + l]);
+        const int4 *ci4 = reinterpret_cast<const int4 *>(cand_i + lbase * kc);
+        const float4 *cs4 = reinterpret_cast<const float4 *>(cand_s + lbase * kc);
         for (int c4 = 0; c4 < C / 4; c4++) { // kc is 8 or 16: C is a multiple of 4, the lists are 16-byte aligned
             const int4 ri = ci4[c4];
             const float4 sc = cs4[c4];
@@ -92,7 +95,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
     const int rounds = STAGED ? __reduce_max_sync(0xffffffffu, cnt) : cnt;
     for (int v = 0; v < rounds; v++) {
         const bool act = v < cnt;
-        const int ri = act ? __ldg(cand_i + qg * C + vlist[v][threadIdx.x]) : 0;
+        const int ri = act ? __ldg(cand_i + lbase * kc + vlist[v][threadIdx.x]) : 0;
         float d;
         if (STAGED) {
             float acc = 0.f;
@@ -132,7 +135,7 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
         }
         if (!act) continue;
         if (audit) { // error-model audit: observed |s~ + ||q16||^2 - d| against the bound the certificate assumes
-            const float sc = __ldg(cand_s + qg * C + vlist[v][threadIdx.x]);
+            const float sc = __ldg(cand_s + lbase * kc + vlist[v][threadIdx.x]);
             const float nsumf = qne[qg] + max_tnorm;
             const float e = tc_band_e(qde[qg], max_dnorm, nsumf), a = tc_band_a(nsumf);
             const float ratio = fabsf(sc + qn16[qg] - d) / (2.f * e * sqrtf(d) + e * e + a);
@@ -191,12 +194,12 @@ __global__ void __launch_bounds__(RR_THREADS) rerank_kernel(
 } // namespace
 
 int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, const float *d_cand_s,
-                     const int *d_cand_i, const float *d_cand_tau, int nsplit, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
+                     const int *d_cand_i, const float *d_cand_tau, const TcPlan &plan, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
                      const float *d_qdnorm, float max_tnorm, float max_dnorm, int k, int *d_idx, float *d_err, int *d_fb_list, int *d_fb_count,
                      cudaStream_t s) {
     const unsigned grid = (unsigned)((nq + RR_THREADS - 1) / RR_THREADS);
     const bool staged = (dd & 3) == 0 && (((uintptr_t)d_q | (uintptr_t)d_rows) & 15) == 0;
-    const int maxv = nsplit * kc > RR_MAXV ? RR_MAXV_WIDE : RR_MAXV;
+    const int maxv = plan.max_nlists() * kc > RR_MAXV ? RR_MAXV_WIDE : RR_MAXV;
     const size_t dyn = (size_t)maxv * RR_THREADS;
     static std::atomic<uint32_t> attr{0}; // per device (tm_first_on_device)
     if (tm_first_on_device(attr)) {
@@ -206,7 +209,7 @@ int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, 
         TM_CUDA(cudaFuncSetAttribute(rerank_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
         TM_CUDA(cudaFuncSetAttribute(rerank_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, wide));
     }
-#define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, dyn, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, nsplit, kc, d_qnorm16, d_qnorm_exact, d_qdnorm, max_tnorm, max_dnorm, k, maxv, d_idx, d_err, d_fb_list, d_fb_count, tm_audit_slots())
+#define RR_LAUNCH(K1, ST) rerank_kernel<K1, ST><<<grid, RR_THREADS, dyn, s>>>(d_rows, dd, d_q, nq, d_cand_s, d_cand_i, d_cand_tau, plan, kc, d_qnorm16, d_qnorm_exact, d_qdnorm, max_tnorm, max_dnorm, k, maxv, d_idx, d_err, d_fb_list, d_fb_count, tm_audit_slots())
     if (k == 1) { if (staged) RR_LAUNCH(true, true); else RR_LAUNCH(true, false); }
     else { if (staged) RR_LAUNCH(false, true); else RR_LAUNCH(false, false); }
 #undef RR_LAUNCH

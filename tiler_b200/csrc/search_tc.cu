@@ -437,10 +437,27 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     if (nsplit < 1) nsplit = 1;
     int tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
     nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
-    const int nlists = 2 * nsplit;
+    TcPlan plan{qblocks, qblocks, nsplit, tiles_per_split, nsplit, tiles_per_split, total_tiles};
+    // Tail (search_tc.h): with one item per block, the blocks beyond the last FULL round of CTA pairs are split finer,
+    // so the last round runs tiles / ns2 + start-up instead of a whole item.  TM_TC_TAIL=0 switches it off (A/B).
+    static const bool tail_on = !(getenv("TM_TC_TAIL") && atoi(getenv("TM_TC_TAIL")) == 0);
+    if (tail_on && !finest_split && nsplit == 1 && nsplit_env <= 0 && qblocks > units) {
+        const int full = (qblocks / units) * units, rem = qblocks - full;
+        if (rem > 0) {
+            int ns2 = std::min(std::min(max_split, units / rem), total_tiles / 4);
+            if (ns2 >= 2) {
+                int tps2 = (total_tiles + ns2 - 1) / ns2;
+                ns2 = (total_tiles + tps2 - 1) / tps2;
+                const double uniform = (double)((qblocks + units - 1) / units) * (total_tiles + 48);
+                const double tailed = (double)(full / units) * (total_tiles + 48) + (double)((rem * ns2 + units - 1) / units) * (tps2 + 48);
+                if (tailed < 0.97 * uniform) { plan.qb1 = full; plan.ns2 = ns2; plan.tps2 = tps2; }
+            }
+        }
+    }
+    const int nlists = plan.max_nlists();
     *nlists_out = nlists;
 
-    int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)nq_pad * nlists * kc, s);
+    int r = ensure_tc_scratch(nq_pad, h->kp, (size_t)plan.total_lists() * kc, s);
     if (r) return r;
     if (!operand_ready && (r = tm_launch_query_operand(h, d_q, nq, nq_pad, g_tc.q16, g_tc.qn16, g_tc.qne, g_tc.qde, s))) return r;
     CUtensorMap tq;
@@ -459,7 +476,7 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     const bool normfree = k == 1 && tiles_per_split >= nf_min && h->rows_f16s != nullptr;
     g_coarse_launches.fetch_add(1, std::memory_order_relaxed);
     int tok = tm_prof_begin(2, s);
-#define TC_ARGS qblocks, nsplit, tiles_per_split, total_tiles, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, g_tc.qde, h->max_norm, h->max_dnorm, k, s
+#define TC_ARGS plan, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, g_tc.qde, h->max_norm, h->max_dnorm, k, s
 #define TC_LAUNCH(NCH, KC, K1) ((K1) && normfree ? launch_tc2<NCH, KC, K1, K1>(tq, tts, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS) \
                                                 : launch_tc2<NCH, KC, K1, false>(tq, tt, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS))
     if (k == 1) r = nch == 1 ? TC_LAUNCH(1, 8, true) : nch == 2 ? TC_LAUNCH(2, 8, true) : TC_LAUNCH(3, 8, true);
@@ -470,7 +487,7 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     tm_prof_end(tok, s);
     if (r) return r;
     tok = tm_prof_begin(3, s);
-    r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, nlists, kc, g_tc.qn16, g_tc.qne,
+    r = tm_launch_rerank(h->rows_f32, h->dd, d_q, nq, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, plan, kc, g_tc.qn16, g_tc.qne,
                          g_tc.qde, h->max_norm, h->max_dnorm, k, d_idx, d_err, g_tc.fb_list, g_tc.fb_count, s);
     tm_prof_end(tok, s);
     if (r) return r;

@@ -17,12 +17,49 @@ __host__ __device__ __forceinline__ float tc_band_e(float qdnorm, float max_dnor
 }
 __host__ __device__ __forceinline__ float tc_band_a(float nsum) { return 3e-5f * nsum * nsum + 1e-6f; }
 
+// ---- work-item plan of one coarse pass ---------------------------------------------------------------------------
+// A work item = (256-query block, row split).  Blocks [0, qb1) are cut into ns1 row splits of tps1 tiles, blocks
+// [qb1, qblocks) - the TAIL, when the block count does not fill the last round of CTA pairs - into ns2 finer
+// splits of tps2 tiles, so that the last round costs a fraction of an item instead of a whole one (a 4-frame batch
+// is 225 blocks on 74 pairs: 3.04 rounds).  Every (query, split, accumulator column half) owns one candidate list;
+// a query of the first part has nl1 = 2 ns1 lists, one of the tail nl2 = 2 ns2, stored back to back.
+struct TcPlan {
+    int qblocks, qb1, ns1, tps1, ns2, tps2, total_tiles;
+    __host__ __device__ int items() const { return qb1 * ns1 + (qblocks - qb1) * ns2; }
+    // item -> (query block, split, first tile, end tile)
+    __host__ __device__ void decode(int item, int &qb, int &sp, int &t0, int &t1) const {
+        int tps;
+        if (item < qb1 * ns1) {
+            qb = item / ns1;
+            sp = item - qb * ns1;
+            tps = tps1;
+        } else {
+            const int j = item - qb1 * ns1;
+            qb = qb1 + j / ns2;
+            sp = j - (j / ns2) * ns2;
+            tps = tps2;
+        }
+        t0 = sp * tps;
+        t1 = t0 + tps < total_tiles ? t0 + tps : total_tiles;
+    }
+    __host__ __device__ int nlists(int64_t q) const { return q < (int64_t)qb1 * 256 ? 2 * ns1 : 2 * ns2; }
+    __host__ __device__ int64_t list_base(int64_t q) const { // index of query q's first list
+        const int64_t q1 = (int64_t)qb1 * 256;
+        return q < q1 ? q * (2 * ns1) : q1 * (2 * ns1) + (q - q1) * (2 * ns2);
+    }
+    __host__ __device__ int64_t total_lists() const { return list_base((int64_t)qblocks * 256); }
+    __host__ __device__ int max_nlists() const {
+        const int a = qb1 > 0 ? ns1 : 0, b = qb1 < qblocks ? ns2 : 0;
+        return 2 * (a > b ? a : b);
+    }
+};
+
 int tm_launch_query_operand(const ANNkdtree *h, const float *d_q, int64_t nq, int64_t nq_pad, __half *d_q16,
                             float *d_qnorm16, float *d_qnorm_exact, float *d_qdnorm, cudaStream_t s);
 int tm_make_query_tmap(void *tmap, const __half *d_q16, int64_t nq_pad, int kp);
 
 // exact float32 re-rank of the coarse candidates + certification (rerank.cu, compiled -fmad=false)
 int tm_launch_rerank(const float *d_rows, int dd, const float *d_q, int64_t nq, const float *d_cand_s,
-                     const int *d_cand_i, const float *d_cand_tau, int nsplit, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
+                     const int *d_cand_i, const float *d_cand_tau, const TcPlan &plan, int kc, const float *d_qnorm16, const float *d_qnorm_exact,
                      const float *d_qdnorm, float max_tnorm, float max_dnorm, int k, int *d_idx, float *d_err, int *d_fb_list, int *d_fb_count,
                      cudaStream_t s);
