@@ -216,6 +216,21 @@ TM_API int tm_kmodes_update_centroids(tm_kmodes *km, const int32_t *h_idx, const
 TM_API int tm_kmodes_assign_range(tm_kmodes *km, int64_t lo, int64_t hi, int32_t *h_clust, uint64_t *h_dis);
 TM_API int tm_kmodes_read_centroids(tm_kmodes *km, uint8_t *h_centroids);
 
+/* Allocation-free variant of tm_kmodes_assign_dev.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library routine and never
+ * synchronises: two kernels are enqueued on cuda_stream (a cudaStream_t; NULL = the default stream) of the
+ * CURRENT device, results are ready when that stream reaches them.  Its scratch (bit-sliced centroids + one
+ * flag word) is a fixed device array inside the library: k <= TM_NOALLOC_MAX_CENTROIDS, larger k is rejected
+ * with TM_EINVAL (tm_last_error says so); npoints is not limited.  The array costs 768.25 KB on every GPU
+ * that loads the library, until exit.  All calls on one GPU share it: calls that overlap on the GPU (streams
+ * without an ordering between them) race; calls on one stream, or ordered by events, are safe.  The first
+ * call on a device resolves the array's device address (cudaGetSymbolAddress): make one call outside a graph
+ * capture first.  Same results as tm_kmodes_assign_dev, bit for bit. */
+#define TM_NOALLOC_MAX_CENTROIDS 16384
+TM_API int tm_kmodes_assign_noalloc(const uint8_t *d_X, int64_t npoints, const uint8_t *d_centroids, int64_t k,
+                                    int semantics, int32_t *d_clust, uint64_t *d_dis, void *cuda_stream);
+
 /* UpdateMinDistance (kmodes.pas:455-596): mindist[i] = min(mindist[i], dissim(center, X[i])) */
 TM_API int tm_kmodes_update_min_distance(const uint8_t *h_X, int64_t npoints,
                                          const uint8_t *h_center, int semantics,

@@ -71,6 +71,7 @@ PROTOTYPES = {
     "tm_kmodes_update_centroids": (i32, [vp, vp, vp, i64]),
     "tm_kmodes_assign_range": (i32, [vp, i64, i64, vp, vp]),
     "tm_kmodes_read_centroids": (i32, [vp, vp]),
+    "tm_kmodes_assign_noalloc": (i32, [vp, i64, vp, i64, i32, vp, vp, vp]),
     "tm_kmodes_update_min_distance": (i32, [vp, i64, vp, i32, vp]),
     "tm_kmodes_farthest_first": (i32, [vp, i64, i64, i64, i32, vp, vp]),
     "tm_kmodes_representatives": (i32, [vp, i64, vp, vp, i64, i32, vp, vp]),

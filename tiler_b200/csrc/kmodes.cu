@@ -562,3 +562,82 @@ int tm_launch_kmodes_rows(const uint8_t *d_palpix, int64_t ntiles, int pal_size,
     tm_count_launch();
     return tm_check(cudaGetLastError(), "kmodes_rows_kernel");
 }
+
+// ---- allocation-free KModes assignment (tm_kmodes_assign_noalloc) ---------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same two kernels as
+// tm_kmodes_assign_dev (kmodes_pack_centroids_kernel -> kmodes_assign_kernel, centroids not split over the grid), but
+// the scratch - the bit-sliced copy of the centroids and the "some byte >= 16" flag - lives in a file-scope device
+// array of fixed size instead of a grow-only cudaMalloc buffer.  Every GPU that loads the library holds the array
+// (TM_NOALLOC_MAX_CENTROIDS x 48 B + 256 B = 768.25 KB) until the process exits.  All calls on a device share it and
+// it keeps the last call's contents: the flag word is cleared at the start of every call (stream-ordered), the
+// bit-sliced rows are rewritten for the k centroids the call uses.  Calls that overlap on the GPU (different streams,
+// no ordering between them) race on it.
+namespace {
+struct __align__(256) KmNoAllocScratch {
+    uint32_t cb[(size_t)TM_NOALLOC_MAX_CENTROIDS * KM_BWORDS]; // bit-sliced centroids
+    int flag[64];                                              // [0] = wide flag; padded to 256 bytes
+};
+static __device__ __align__(256) KmNoAllocScratch g_km_noalloc; // in HOST code this name is a stand-in, not a device address
+
+std::mutex g_km_noalloc_mu;
+KmNoAllocScratch *g_km_noalloc_ptr[TM_MAX_DEV] = {}; // device address of g_km_noalloc on each device (cudaGetSymbolAddress)
+
+// once per device, with that device current
+int km_noalloc_scratch(int dev, KmNoAllocScratch **out) {
+    std::lock_guard<std::mutex> lk(g_km_noalloc_mu);
+    if (!g_km_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_km_noalloc);
+        if (e != cudaSuccess || !p) {
+            tm_set_error("tm_kmodes_assign_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return TM_ECUDA;
+        }
+        g_km_noalloc_ptr[dev] = static_cast<KmNoAllocScratch *>(p);
+    }
+    *out = g_km_noalloc_ptr[dev];
+    return 0;
+}
+} // namespace
+
+extern "C" int tm_kmodes_assign_noalloc(const uint8_t *d_X, int64_t npoints, const uint8_t *d_centroids, int64_t k, int semantics,
+                                        int32_t *d_clust, uint64_t *d_dis, void *cuda_stream) {
+    if (semantics != TM_KM_ASM && semantics != TM_KM_GENERIC) { tm_set_error("unknown KModes semantics %d", semantics); return TM_EINVAL; }
+    if (npoints < 0 || k < 0 || (npoints && (!d_X || !d_clust)) || (k && !d_centroids)) {
+        tm_set_error("tm_kmodes_assign_noalloc: bad arguments");
+        return TM_EINVAL;
+    }
+    if (k > TM_NOALLOC_MAX_CENTROIDS) {
+        tm_set_error("tm_kmodes_assign_noalloc: %lld centroids exceed the fixed scratch (TM_NOALLOC_MAX_CENTROIDS = %d); "
+                     "use tm_kmodes_assign_dev", (long long)k, TM_NOALLOC_MAX_CENTROIDS);
+        return TM_EINVAL;
+    }
+    if (npoints > 0x7fffffffll * 256) { tm_set_error("tm_kmodes_assign_noalloc: too many points"); return TM_EINVAL; }
+    if (((uintptr_t)d_X & 15) || ((uintptr_t)d_centroids & 15)) { tm_set_error("KModes rows must be 16-byte aligned"); return TM_EINVAL; }
+    if (npoints == 0) return 0;
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= TM_MAX_DEV) {
+        cudaGetLastError();
+        tm_set_error("tm_kmodes_assign_noalloc: no current CUDA device");
+        return TM_ENODEVICE;
+    }
+    KmNoAllocScratch *sc = nullptr;
+    int r = km_noalloc_scratch(dev, &sc);
+    if (r) return r;
+    cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+    TM_CUDA(cudaMemsetAsync(sc->flag, 0, sizeof(int), s)); // must start at zero: the pack kernel only ever sets it
+    if (k > 0) {
+        kmodes_pack_centroids_kernel<<<(unsigned)((k + 127) / 128), 128, 0, s>>>((const uint32_t *)d_centroids, k, sc->cb, sc->flag);
+        tm_count_launch();
+    }
+    const dim3 grid((unsigned)((npoints + 255) / 256), 1);
+    const int64_t cchunk = k > 0 ? k : 1;
+    if (semantics == TM_KM_ASM)
+        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, npoints, (const uint32_t *)d_centroids, k, sc->cb,
+                                                             sc->flag, d_clust, d_dis, cchunk, nullptr, nullptr);
+    else
+        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, npoints, (const uint32_t *)d_centroids, k,
+                                                                 sc->cb, sc->flag, d_clust, d_dis, cchunk, nullptr, nullptr);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "tm_kmodes_assign_noalloc");
+}
