@@ -64,6 +64,8 @@ def parse():
     ap.add_argument("--no-kernels", action="store_true", help="skip the secondary-kernel block (`kernels`)")
     ap.add_argument("--no-extras", action="store_true", help="skip the unplanted-query pass and the call-pattern block")
     ap.add_argument("--frames", type=int, default=0, help="override the clip length (profiling runs only)")
+    ap.add_argument("--tiles", type=int, default=0, help="override the tileset size (experiments only)")
+    ap.add_argument("--k", type=int, default=0, help="override k (experiments only)")
     return ap.parse_args()
 
 
@@ -638,7 +640,11 @@ def run_b200(args, rank, world, local_rank):
     import tiler_b200 as tb
     from tiler_b200.shard import ShardedFrameTiling, frame_shards
 
-    wl = WORKLOADS[name_wl]
+    wl = dict(WORKLOADS[name_wl])
+    if args.tiles:
+        wl["tiles"] = args.tiles
+    if args.k:
+        wl["k"] = args.k
     k = wl["k"]
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
