@@ -457,7 +457,9 @@ def helper_kernels(torch, tb, dev, stream, hbm_gbs, reps=3):
     import ctypes as _C
     with tb.KModesState(Xh) as stt:
         stt.set_centroids(Ch)
-        stt.assign_range(0, 960)
+        # the initial whole-set assignment of ComputeKModes (kmodes.pas:984-997) through the handle: KModesIter's bins
+        # then start from every point's previous label as a bound, as every pass after the first does
+        stt.assign_range(0, npnt)
         cl, di = np.empty(960, np.int32), np.empty(960, np.uint64)
         idx = rng.integers(0, k, (1100, 4)).astype(np.int32)
         rows = np.ascontiguousarray(Ch[idx])  # [1100][4][80]
@@ -470,7 +472,8 @@ def helper_kernels(torch, tb, dev, stream, hbm_gbs, reps=3):
             nb += 1
         dt = time.perf_counter() - t0
     out["kmodes_iter_c4_handle"] = {"bins": nb, "ms": 1e3 * dt, "us_per_bin": 1e6 * dt / nb, "pairs_per_s": npnt * k / dt,
-                                    "note": "tm_kmodes_update_centroids (4 rows) + tm_kmodes_assign_range per 960-point bin"}
+                                    "note": "tm_kmodes_update_centroids (4 rows) + tm_kmodes_assign_range per 960-point bin, after the initial "
+                                            "whole-set assignment through the same handle"}
     return out
 
 

@@ -204,7 +204,10 @@ TM_API int tm_kmodes_assign_dev(const uint8_t *d_X, int64_t npoints, const uint8
 /* Device-resident KModes state for the per-bin loop of KModesIter (kmodes.pas:845-909): the points are
  * uploaded once, the centroids stay on the device, the caller sends only the rows MovePointCat changed
  * (kmodes.pas:778-806) between two 960-point bins and gets one bin's (clust, dis) per call.  Same kernel,
- * same results as tm_kmodes_assign; no allocation and one synchronisation per bin. */
+ * same results as tm_kmodes_assign.  A bin-sized call allocates nothing, issues one or two kernel launches and no copy
+ * command: results arrive in pinned host memory and the call polls a completion flag (TM_KM_POLL=0: copy + synchronise).
+ * The handle remembers every point's last label and uses it as a bound for the next call on that point (a bound only:
+ * results never depend on it). */
 typedef struct tm_kmodes tm_kmodes;
 TM_API tm_kmodes *tm_kmodes_open(const uint8_t *h_X, int64_t npoints, int semantics);
 TM_API void tm_kmodes_close(tm_kmodes *km);

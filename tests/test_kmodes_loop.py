@@ -99,3 +99,42 @@ def test_kmodes_handle_matches_one_shot_calls(oracle):
             st.update_centroids(np.array([len(C)], np.int32), rows[:1])
         with pytest.raises(Exception):
             st.assign_range(0, 5001)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("m", [5, 24, 25, 300])
+def test_kmodes_handle_updates_with_duplicates_last_row_wins(oracle, m):
+    """tm_kmodes_update_centroids with repeated centroid indices behaves like sequential stores, through the rows-in-
+    kernel-parameters path (m <= 24) and the staged path; bin-sized ranges (results polled from mapped host memory)
+    and a whole-set range (copied) see the same centroids."""
+    import tiler_b200 as tb
+    o = oracle
+    X = _rows(o, 4000, 123 + m)
+    C = X[::10].copy()                             # 400 centroids: bin-sized calls split them over the grid
+    rng = np.random.default_rng(m)
+    idx = rng.integers(0, 40, m).astype(np.int32)  # few distinct targets: many duplicates
+    rows = X[rng.integers(0, 4000, m)].copy()
+    C2 = C.copy()
+    for i in range(m):
+        C2[idx[i]] = rows[i]
+    with tb.KModesState(X) as st:
+        st.set_centroids(C)
+        st.update_centroids(idx, rows)
+        assert np.array_equal(st.centroids(), C2)
+        for lo, hi in [(0, 960), (960, 1920), (0, 4000), (3999, 4000)]:
+            gc, gd = st.assign_range(lo, hi)
+            wc, wd = o.kmodes_assign(X[lo:hi], C2)
+            assert np.array_equal(gc, wc) and np.array_equal(gd, wd)
+        gc, _ = st.assign_range(0, 960, with_dis=False)
+        assert np.array_equal(gc, o.kmodes_assign(X[:960], C2)[0])
+        # two updates and two bins back to back: the staging of the first is still in flight when the second lands
+        st.update_centroids(idx[::-1].copy(), rows[::-1].copy())
+        st.update_centroids(idx[:3], rows[:3])
+        C3 = C2.copy()
+        for i in range(m - 1, -1, -1):
+            C3[idx[i]] = rows[i]
+        for i in range(3):
+            C3[idx[i]] = rows[i]
+        gc, gd = st.assign_range(1000, 1960)
+        wc, wd = o.kmodes_assign(X[1000:1960], C3)
+        assert np.array_equal(gc, wc) and np.array_equal(gd, wd)

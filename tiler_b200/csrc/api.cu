@@ -7,6 +7,8 @@
 #include <chrono>
 #include <algorithm>
 #include <vector>
+#include <unordered_map>
+#include <atomic>
 #include <string>
 #include <thread>
 #include <dlfcn.h>

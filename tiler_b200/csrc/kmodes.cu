@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *_
                                                              int32_t *__restrict__ clust,
                                                              uint64_t *__restrict__ dis, int64_t cchunk,
                                                              int32_t *__restrict__ part_i,
-                                                             uint32_t *__restrict__ part_d) {
+                                                             uint32_t *__restrict__ part_d, const TmKmHostOut bin) {
     // blockIdx.y selects a range of cchunk centroids (few points: the centroids are split over the grid and
     // merged by kmodes_merge_kernel; gridDim.y == 1: the whole set, results written directly)
     const int64_t c_lo = (int64_t)blockIdx.y * cchunk, c_hi = min(k, c_lo + cchunk);
@@ -182,6 +182,15 @@ __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *_
     const bool fast = !__syncthreads_or((wide & 0xf0f0f0f0u) != 0) && *cent_wide == 0; // block-uniform
     uint32_t best = 0xffffffffu;
     int bi = -1;
+    if (bin.prev && i < np) {
+        // Bin-sized call with a finer centroid split: every block would start without a bound and evaluate the byte-wise
+        // SAD term for each record of its own short range (some lane of a warp does so in nine iterations out of ten).
+        // The point's label from the previous pass gives the bound at once - labels rarely change between two
+        // KModesIter passes.  Only a bound: bi stays -1 until a centroid of THIS range reaches it (the previous
+        // centroid itself does, in its own range), so results do not depend on it.
+        const int pi = bin.prev[i];
+        if (pi >= 0 && pi < k) best = dissim_words<SEM>(p, C + (int64_t)pi * KM_WORDS);
+    }
     if (fast) {
         uint32_t pb[KM_BWORDS];
         bitslice_row(p, pb);
@@ -226,6 +235,38 @@ __global__ void __launch_bounds__(256, 3) kmodes_assign_kernel(const uint32_t *_
             }
         }
     }
+    if (bin.keys) {
+        // KModes handle, bin-sized call (tm_kmodes_assign_range): the centroid ranges meet in one 64-bit atomicMin per
+        // point - (dissimilarity, ~index): the smallest dissimilarity, the LAST index among equals - and the last
+        // block of the grid to finish writes labels and dissimilarities straight into mapped host memory, re-arms
+        // the keys for the next call and publishes the call's sequence number in a host flag the caller polls: no
+        // merge launch, no copy command, no stream synchronisation per bin.
+        if (i < np && bi >= 0)
+            atomicMin(bin.keys + i, ((unsigned long long)best << 32) | (unsigned long long)(0xffffffffu - (uint32_t)bi));
+        __shared__ bool last;
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) last = atomicAdd(bin.d_done, 1u) == gridDim.x * gridDim.y - 1;
+        __syncthreads();
+        if (!last) return;
+        __threadfence();
+        for (int64_t j = threadIdx.x; j < np; j += blockDim.x) {
+            const unsigned long long key = __ldcg(bin.keys + j);
+            bin.keys[j] = ~0ull;
+            const bool have = key != ~0ull;
+            const int32_t lab = have ? (int32_t)(0xffffffffu - (uint32_t)key) : -1;
+            bin.m_clust[j] = lab;
+            if (bin.prev) bin.prev[j] = lab;
+            if (bin.m_dis) bin.m_dis[j] = have ? (uint64_t)(key >> 32) : ~(uint64_t)0;
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            *bin.d_done = 0;
+            *reinterpret_cast<volatile int *>(bin.m_flag) = bin.seq;
+        }
+        return;
+    }
     if (i < np) {
         if (gridDim.y > 1) {
             part_i[(int64_t)blockIdx.y * np + i] = bi;
@@ -251,6 +292,35 @@ __global__ void kmodes_merge_kernel(const int32_t *__restrict__ part_i, const ui
     }
     clust[i] = bi;
     if (dis) dis[i] = (uint64_t)best;
+}
+
+// changed centroid rows carried in the kernel's parameter space (MovePointCat touches a handful per bin): no staging copy
+constexpr int KM_INLINE_ROWS = 24;
+struct KmInlineRows {
+    int32_t idx[KM_INLINE_ROWS];
+    uint32_t rows[KM_INLINE_ROWS][KM_WORDS];
+};
+__global__ void kmodes_update_inline_kernel(const __grid_constant__ KmInlineRows u, int m, int64_t k, uint32_t *__restrict__ C,
+                                            uint32_t *__restrict__ Cb, int *__restrict__ wide_flag) {
+    const int i = threadIdx.x;
+    if (i >= m) return;
+    // duplicates: the LAST row for a centroid wins, like sequential stores - earlier ones step aside
+    for (int j = i + 1; j < m; j++)
+        if (u.idx[j] == u.idx[i]) return;
+    const int64_t c = u.idx[i];
+    if (c < 0 || c >= k) return; // validated on the host
+    uint32_t p[KM_WORDS], wide = 0;
+#pragma unroll
+    for (int w = 0; w < KM_WORDS; w++) {
+        p[w] = u.rows[i][w];
+        C[c * KM_WORDS + w] = p[w];
+        wide |= p[w];
+    }
+    if (wide & 0xf0f0f0f0u) atomicOr(wide_flag, 1);
+    uint32_t o[KM_BWORDS];
+    bitslice_row(p, o);
+#pragma unroll
+    for (int w = 0; w < KM_BWORDS; w++) Cb[c * KM_BWORDS + w] = o[w];
 }
 
 template <int SEM>
@@ -441,10 +511,44 @@ int tm_kmodes_update_packed(TmKmScratch &c, uint8_t *d_c, int64_t k, const uint8
     return tm_check(cudaGetLastError(), "kmodes_update_centroids_kernel");
 }
 
+int tm_kmodes_inline_rows() { return KM_INLINE_ROWS; }
+// m <= KM_INLINE_ROWS changed rows from HOST memory through the kernel's parameters
+int tm_kmodes_update_inline(TmKmScratch &c, uint8_t *d_c, int64_t k, const uint8_t *h_rows, const int32_t *h_idx, int m,
+                            cudaStream_t s) {
+    if (m == 0) return 0;
+    KmInlineRows u;
+    memcpy(u.idx, h_idx, sizeof(int32_t) * (size_t)m);
+    memcpy(u.rows, h_rows, (size_t)m * 80);
+    kmodes_update_inline_kernel<<<1, 32, 0, s>>>(u, m, k, (uint32_t *)d_c, c.cb, c.flag);
+    tm_count_launch();
+    return tm_check(cudaGetLastError(), "kmodes_update_inline_kernel");
+}
+
 // assignment of np points against centroids already packed in c
 int tm_kmodes_assign_packed(TmKmScratch &c, const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
-                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s) {
+                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s, const TmKmHostOut *ho, bool *ho_used) {
+    if (ho_used) *ho_used = false;
     if (np == 0) return 0;
+    if (ho && ho->keys && np <= ho->keys_cap && k >= 1 && (np + 255) / 256 < 2 * tm_num_sms()) {
+        // Bin-sized call through the handle.  The whole-set split below cuts the centroids in multiples of the 512-row
+        // shared-memory tile: a 960-point bin against 16 384 centroids is then 4 x 32 = 128 blocks of 8 warps, one per
+        // SM, latency-bound (96 us under ncu).  Here the ranges are as fine as one wave of 3 blocks per SM allows
+        // (16-centroid granularity) and meet in an atomicMin per point instead of a partial-result array.
+        const unsigned gxb = (unsigned)((np + 255) / 256);
+        int64_t want = (3 * (int64_t)tm_num_sms() + gxb - 1) / gxb; // ranges per row of blocks
+        if (want < 1) want = 1;
+        int64_t chunk = ((k + want - 1) / want + 15) & ~(int64_t)15;
+        if (chunk < 16) chunk = 16;
+        const unsigned partsb = (unsigned)((k + chunk - 1) / chunk);
+        const dim3 gridb(gxb, partsb);
+        if (sem == TM_KM_ASM)
+            kmodes_assign_kernel<TM_KM_ASM><<<gridb, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, nullptr, nullptr, chunk, nullptr, nullptr, *ho);
+        else
+            kmodes_assign_kernel<TM_KM_GENERIC><<<gridb, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, nullptr, nullptr, chunk, nullptr, nullptr, *ho);
+        tm_count_launch();
+        if (ho_used) *ho_used = true;
+        return tm_check(cudaGetLastError(), "kmodes_assign_kernel(bin)");
+    }
     const unsigned gx = (unsigned)((np + 255) / 256);
     // Few points (KModesIter's bins of 960, kmodes.pas:847): thread-per-point alone would occupy a handful of SMs,
     // so the centroids are split over gridDim.y in multiples of the shared-memory tile and merged afterwards.
@@ -468,10 +572,11 @@ int tm_kmodes_assign_packed(TmKmScratch &c, const uint8_t *d_X, int64_t np, cons
         }
     }
     const dim3 grid(gx, (unsigned)parts);
+    const TmKmHostOut none{};
     if (sem == TM_KM_ASM)
-        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, d_clust, d_dis, cchunk, c.part_i, c.part_d);
+        kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, d_clust, d_dis, cchunk, c.part_i, c.part_d, none);
     else
-        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, d_clust, d_dis, cchunk, c.part_i, c.part_d);
+        kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, np, (const uint32_t *)d_c, k, c.cb, c.flag, d_clust, d_dis, cchunk, c.part_i, c.part_d, none);
     if (parts > 1) {
         kmodes_merge_kernel<<<gx, 256, 0, s>>>(c.part_i, c.part_d, np, parts, d_clust, d_dis);
         tm_count_launch();
@@ -634,10 +739,10 @@ extern "C" int tm_kmodes_assign_noalloc(const uint8_t *d_X, int64_t npoints, con
     const int64_t cchunk = k > 0 ? k : 1;
     if (semantics == TM_KM_ASM)
         kmodes_assign_kernel<TM_KM_ASM><<<grid, 256, 0, s>>>((const uint32_t *)d_X, npoints, (const uint32_t *)d_centroids, k, sc->cb,
-                                                             sc->flag, d_clust, d_dis, cchunk, nullptr, nullptr);
+                                                             sc->flag, d_clust, d_dis, cchunk, nullptr, nullptr, TmKmHostOut{});
     else
         kmodes_assign_kernel<TM_KM_GENERIC><<<grid, 256, 0, s>>>((const uint32_t *)d_X, npoints, (const uint32_t *)d_centroids, k,
-                                                                 sc->cb, sc->flag, d_clust, d_dis, cchunk, nullptr, nullptr);
+                                                                 sc->cb, sc->flag, d_clust, d_dis, cchunk, nullptr, nullptr, TmKmHostOut{});
     tm_count_launch();
     return tm_check(cudaGetLastError(), "tm_kmodes_assign_noalloc");
 }

@@ -205,8 +205,25 @@ int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, 
 int tm_kmodes_pack_centroids(TmKmScratch &c, const uint8_t *d_c, int64_t k, cudaStream_t s);
 int tm_kmodes_update_packed(TmKmScratch &c, uint8_t *d_c, int64_t k, const uint8_t *d_rows, const int32_t *d_idx, int64_t m,
                             int *d_bad, cudaStream_t s);
+// optional completion through mapped host memory (KModes handle): merged results + the call's sequence number in *m_flag
+struct TmKmHostOut {
+    unsigned long long *keys = nullptr; // [keys_cap] device, all ~0 between calls: (dissimilarity << 32 | ~index) per point
+    int64_t keys_cap = 0;
+    int32_t *prev = nullptr;            // [np] labels of these points from the previous pass (-1: none): read as a bound, rewritten
+    int32_t *m_clust = nullptr;         // device-visible addresses of page-locked host buffers
+    uint64_t *m_dis = nullptr;          // may be NULL
+    unsigned int *d_done = nullptr;     // device counter, zero between calls
+    int *m_flag = nullptr;
+    int seq = 0;
+};
+// ho != NULL and the call is bin-sized (fewer blocks of points than two per SM, np <= ho->keys_cap): the centroid ranges
+// meet in ho->keys, results go to ho->m_clust / m_dis, *ho_used = true; otherwise to d_clust / d_dis as before
 int tm_kmodes_assign_packed(TmKmScratch &c, const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
-                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s);
+                            int32_t *d_clust, uint64_t *d_dis, cudaStream_t s, const TmKmHostOut *ho = nullptr,
+                            bool *ho_used = nullptr);
+int tm_kmodes_inline_rows();
+int tm_kmodes_update_inline(TmKmScratch &c, uint8_t *d_c, int64_t k, const uint8_t *h_rows, const int32_t *h_idx, int m,
+                            cudaStream_t s);
 void tm_kmodes_scratch_free(TmKmScratch &c);
 int tm_launch_kmodes_farthest_first(const uint8_t *d_X, int64_t np, int64_t k, int64_t init_point, int sem,
                                     uint8_t *d_centroids, int64_t *d_chosen, unsigned long long *d_argkey,
