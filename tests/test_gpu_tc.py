@@ -261,3 +261,25 @@ def test_tc_long_items_equal_exact_engine(tb, oracle, k):
     assert st["fallback_queries"] < nq // 20, st
     oi, od = oracle.knn_f32(ds, q[:32], k)
     assert np.array_equal(te[:32].view(np.uint32), od.view(np.uint32))
+
+
+@pytest.mark.parametrize("k", [2, 8])
+def test_tc_chained_plan_equals_exact_engine(k):
+    """k > 1 against a tileset beyond the L2: the rows are cut into splits, the work items run split-major and every
+    item starts from the threshold its query block reached in the previous split (search_tc.h: TcPlan.chain).  Forced
+    here on 131 072 rows with TM_TC_CHAIN=2 in a process of its own (the switch is read once); TM_TC_CHAIN=0 in a
+    second process must give the same, exact, answer."""
+    import json
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    for chain in ("2", "0"):
+        env = dict(os.environ, TM_TC_CHAIN=chain)
+        out = subprocess.run([sys.executable, os.path.join(here, "chain_check.py"), str(k)], env=env, capture_output=True,
+                             text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        res = json.loads(out.stdout.strip().splitlines()[-1])
+        assert res["idx_equal"] and res["err_equal"], (chain, res)
+        assert res["coarse_launches"] > 0, res
+        assert res["fallback_queries"] < res["nq"] // 10, (chain, res)

@@ -437,11 +437,31 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     if (nsplit < 1) nsplit = 1;
     int tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
     nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
-    TcPlan plan{qblocks, qblocks, nsplit, tiles_per_split, nsplit, tiles_per_split, total_tiles};
+    // k > 1 against a tileset whose operand does not fit the L2 (C5: 1 048 576 rows = 403 MB): one item per query block
+    // lets the CTA pairs drift apart along the scan until every tile comes from HBM again for most of them (ncu, 1 M x
+    // 1 M: 539 GB read, L2 hit rate 67 %, and the SM clock sinks under the power cap).  Chained plan: the rows are cut
+    // into L2-sized splits and the items run split-major, each continuing the candidate lists and the threshold of its
+    // query block's previous split (search_tc.h), so all pairs share one stretch of the operand and a query still has
+    // one list per column half.  TM_TC_CHAIN=0 switches it off (A/B).
+    int chain = 0;
+    static const int chain_env = getenv("TM_TC_CHAIN") ? atoi(getenv("TM_TC_CHAIN")) : 1;
+    if (k > 1 && chain_env && !finest_split && nsplit == 1 && nsplit_env <= 0 && qblocks >= 4 * units) {
+        const double op_mb = (double)h->n_pad * h->kp * 2.0 / 1048576.0;
+        const int target_mb = chain_env > 1 ? chain_env : 48; // operand bytes per split (TM_TC_CHAIN=<MB> to tune)
+        int ns = (int)((op_mb + target_mb - 1) / target_mb);
+        if (ns > max_split) ns = max_split;
+        if (ns >= 2 && total_tiles / ns >= 64) {
+            chain = 1;
+            nsplit = ns;
+            tiles_per_split = (total_tiles + nsplit - 1) / nsplit;
+            nsplit = (total_tiles + tiles_per_split - 1) / tiles_per_split;
+        }
+    }
+    TcPlan plan{qblocks, qblocks, nsplit, tiles_per_split, nsplit, tiles_per_split, total_tiles, chain};
     // Tail (search_tc.h): with one item per block, the blocks beyond the last FULL round of CTA pairs are split finer,
     // so the last round runs tiles / ns2 + start-up instead of a whole item.  TM_TC_TAIL=0 switches it off (A/B).
     static const bool tail_on = !(getenv("TM_TC_TAIL") && atoi(getenv("TM_TC_TAIL")) == 0);
-    if (tail_on && !finest_split && nsplit == 1 && nsplit_env <= 0 && qblocks > units) {
+    if (tail_on && !chain && !finest_split && nsplit == 1 && nsplit_env <= 0 && qblocks > units) {
         const int full = (qblocks / units) * units, rem = qblocks - full;
         if (rem > 0) {
             int ns2 = std::min(std::min(max_split, units / rem), total_tiles / 4);
@@ -466,6 +486,17 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     const CUtensorMap &tn = static_cast<const CUtensorMap *>(h->tmap_rows)[1];
     const CUtensorMap &tts = static_cast<const CUtensorMap *>(h->tmap_rows)[2]; // k = 1: operand in scan order
     TM_CUDA(cudaMemsetAsync(g_tc.fb_count, 0, sizeof(int), s));
+    if (chain) { // per query block: epilogue warps that have finished a split of it (search_tc2_kernel.inc)
+        if ((size_t)qblocks > g_tc.cap_ready) {
+            cudaStreamSynchronize(s);
+            cudaFree(g_tc.chain_ready);
+            g_tc.chain_ready = nullptr; g_tc.cap_ready = 0;
+            const size_t cap = (size_t)qblocks + (size_t)qblocks / 2;
+            TM_CUDA(cudaMalloc(&g_tc.chain_ready, sizeof(int) * cap));
+            g_tc.cap_ready = cap;
+        }
+        TM_CUDA(cudaMemsetAsync(g_tc.chain_ready, 0, sizeof(int) * (size_t)qblocks, s));
+    }
     // k = 1, long work items: norm-free accumulator over the operand in scan order (search_tc2_kernel.inc).  Its slow
     // path costs more per call and an item starts on a tile of one norm level, so it needs long items, longer ones when
     // the queries come in the caller's order (many slow-path calls).  Same-box A/B: sorted batch, 256 tiles per item
@@ -476,7 +507,7 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     const bool normfree = k == 1 && tiles_per_split >= nf_min && h->rows_f16s != nullptr;
     g_coarse_launches.fetch_add(1, std::memory_order_relaxed);
     int tok = tm_prof_begin(2, s);
-#define TC_ARGS plan, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, g_tc.qde, h->max_norm, h->max_dnorm, k, s
+#define TC_ARGS plan, g_tc.cand_s, g_tc.cand_i, g_tc.cand_tau, g_tc.qn16, g_tc.qne, g_tc.qde, h->max_norm, h->max_dnorm, k, g_tc.chain_ready, s
 #define TC_LAUNCH(NCH, KC, K1) ((K1) && normfree ? launch_tc2<NCH, KC, K1, K1>(tq, tts, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS) \
                                                 : launch_tc2<NCH, KC, K1, false>(tq, tt, tn, h->norm_scale, h->norms_s, h->perm, TC_ARGS))
     if (k == 1) r = nch == 1 ? TC_LAUNCH(1, 8, true) : nch == 2 ? TC_LAUNCH(2, 8, true) : TC_LAUNCH(3, 8, true);

@@ -23,13 +23,21 @@ __host__ __device__ __forceinline__ float tc_band_a(float nsum) { return 3e-5f *
 // splits of tps2 tiles, so that the last round costs a fraction of an item instead of a whole one (a 4-frame batch
 // is 225 blocks on 74 pairs: 3.04 rounds).  Every (query, split, accumulator column half) owns one candidate list;
 // a query of the first part has nl1 = 2 ns1 lists, one of the tail nl2 = 2 ns2, stored back to back.
+// chain != 0 (k > 1, tilesets beyond the L2, no tail): the items run SPLIT-major - every query block's split 0, then
+// every block's split 1, ... - so that all CTA pairs scan the same L2-sized stretch of the operand at the same time,
+// and an item CONTINUES the candidate lists and the admission threshold its query block reached in the previous split
+// (search_tc2_kernel.inc): a query then has one list per column half, as with a single split.
 struct TcPlan {
-    int qblocks, qb1, ns1, tps1, ns2, tps2, total_tiles;
+    int qblocks, qb1, ns1, tps1, ns2, tps2, total_tiles, chain;
     __host__ __device__ int items() const { return qb1 * ns1 + (qblocks - qb1) * ns2; }
     // item -> (query block, split, first tile, end tile)
     __host__ __device__ void decode(int item, int &qb, int &sp, int &t0, int &t1) const {
         int tps;
-        if (item < qb1 * ns1) {
+        if (chain) { // split-major; qb1 == qblocks
+            sp = item / qblocks;
+            qb = item - sp * qblocks;
+            tps = tps1;
+        } else if (item < qb1 * ns1) {
             qb = item / ns1;
             sp = item - qb * ns1;
             tps = tps1;
@@ -42,13 +50,15 @@ struct TcPlan {
         t0 = sp * tps;
         t1 = t0 + tps < total_tiles ? t0 + tps : total_tiles;
     }
-    __host__ __device__ int nlists(int64_t q) const { return q < (int64_t)qb1 * 256 ? 2 * ns1 : 2 * ns2; }
+    __host__ __device__ int nlists(int64_t q) const { return chain ? 2 : q < (int64_t)qb1 * 256 ? 2 * ns1 : 2 * ns2; }
     __host__ __device__ int64_t list_base(int64_t q) const { // index of query q's first list
         const int64_t q1 = (int64_t)qb1 * 256;
+        if (chain) return q * 2;
         return q < q1 ? q * (2 * ns1) : q1 * (2 * ns1) + (q - q1) * (2 * ns2);
     }
     __host__ __device__ int64_t total_lists() const { return list_base((int64_t)qblocks * 256); }
     __host__ __device__ int max_nlists() const {
+        if (chain) return 2;
         const int a = qb1 > 0 ? ns1 : 0, b = qb1 < qblocks ? ns2 : 0;
         return 2 * (a > b ? a : b);
     }

@@ -105,6 +105,8 @@ struct TmTcScratch { // tensor-core engine: query operand, norms, candidate list
     float *qn16 = nullptr, *qne = nullptr, *qde = nullptr, *cand_s = nullptr, *cand_tau = nullptr;
     int *cand_i = nullptr, *fb_list = nullptr, *fb_count = nullptr;
     int *h_count = nullptr; // pinned
+    int *chain_ready = nullptr; // chained plan: per query block, epilogue warps done (search_tc.cu)
+    size_t cap_ready = 0;
     size_t cap_q = 0, cap_c = 0;
     int kp = 0;
 };
