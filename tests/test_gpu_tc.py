@@ -263,12 +263,13 @@ def test_tc_long_items_equal_exact_engine(tb, oracle, k):
     assert np.array_equal(te[:32].view(np.uint32), od.view(np.uint32))
 
 
-@pytest.mark.parametrize("k", [2, 8])
-def test_tc_chained_plan_equals_exact_engine(k):
-    """k > 1 against a tileset beyond the L2: the rows are cut into splits, the work items run split-major and every
-    item starts from the threshold its query block reached in the previous split (search_tc.h: TcPlan.chain).  Forced
-    here on 131 072 rows with TM_TC_CHAIN=2 in a process of its own (the switch is read once); TM_TC_CHAIN=0 in a
-    second process must give the same, exact, answer."""
+@pytest.mark.parametrize("k,nf_min", [(1, "32"), (1, "1000000"), (2, None), (8, None)])
+def test_tc_chained_plan_equals_exact_engine(k, nf_min):
+    """Tilesets beyond the L2: the rows are cut into splits, the work items run split-major and every item continues
+    the candidate lists and the threshold its query block reached in the previous split (search_tc.h: TcPlan.chain;
+    k = 1: the candidate ring, with the norm-free kernel over the scan-order operand - TM_TC_NF_MIN=32 - and with the
+    norm MMA).  Forced here on 131 072 rows with TM_TC_CHAIN=2 in a process of its own (the switches are read once);
+    TM_TC_CHAIN=0 in a second process must give the same, exact, answer."""
     import json
     import os
     import subprocess
@@ -276,6 +277,8 @@ def test_tc_chained_plan_equals_exact_engine(k):
     here = os.path.dirname(os.path.abspath(__file__))
     for chain in ("2", "0"):
         env = dict(os.environ, TM_TC_CHAIN=chain)
+        if nf_min:
+            env["TM_TC_NF_MIN"] = nf_min
         out = subprocess.run([sys.executable, os.path.join(here, "chain_check.py"), str(k)], env=env, capture_output=True,
                              text=True, timeout=600)
         assert out.returncode == 0, out.stderr[-2000:]

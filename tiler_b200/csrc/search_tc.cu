@@ -445,11 +445,12 @@ static int tc_core(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx
     // one list per column half.  TM_TC_CHAIN=0 switches it off (A/B).
     int chain = 0;
     static const int chain_env = getenv("TM_TC_CHAIN") ? atoi(getenv("TM_TC_CHAIN")) : 1;
-    if (k > 1 && chain_env && !finest_split && nsplit == 1 && nsplit_env <= 0 && qblocks >= 4 * units) {
+    static const int chain_k1 = getenv("TM_TC_CHAIN_K1") ? atoi(getenv("TM_TC_CHAIN_K1")) : 1; // k = 1 as well (A/B)
+    if ((k > 1 || chain_k1) && chain_env && !finest_split && nsplit == 1 && nsplit_env <= 0 && qblocks >= 4 * units) {
         const double op_mb = (double)h->n_pad * h->kp * 2.0 / 1048576.0;
         const int target_mb = chain_env > 1 ? chain_env : 48; // operand bytes per split (TM_TC_CHAIN=<MB> to tune)
         int ns = (int)((op_mb + target_mb - 1) / target_mb);
-        if (ns > max_split) ns = max_split;
+        if (ns > 32) ns = 32; // a query keeps one list per column half whatever the number of splits
         if (ns >= 2 && total_tiles / ns >= 64) {
             chain = 1;
             nsplit = ns;
