@@ -16,7 +16,12 @@ timeout 600 python bench.py --workload c5_4k_2000f_256k_k8 --steps 2 --warmup 1 
 timeout 300 python bench.py --workload c4_kmodes_1m_16k > $O/bench_c4.json 2> $O/bench_c4.err
 timeout 300 python bench.py --workload c1_320x240_64f_4k --steps 20 --warmup 5 --no-kernels --no-extras > $O/bench_c1.json 2> $O/bench_c1.err
 g++ -O2 -std=c++17 scripts/host_threads_bench.cpp -o /tmp/htb -ldl -lpthread && timeout 300 /tmp/htb tiler_b200/libtmann.so > $O/htb.json 2> $O/htb.err
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv \
+timeout 300 /tmp/htb tiler_b200/libtmann.so 65536 32400 > $O/htb_1080.json 2> $O/htb_1080.err
+timeout 300 python scripts/km_iter_bench.py 4 > $O/km_iter.json 2> $O/km_iter.err
+# launch list of the bench command, restricted to the library's kernels (+ the CUB sort it calls): the synthetic
+# inputs come from the reference LCG evaluated with torch, whose thousands of small generator launches would fill -c 400
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_lib.csv \
+    -k regex:"tc2_search|psyv_|rerank_|query_key|invert_order|scatter_|DeviceRadixSort|operand_kernel|gather_rows|search_simt|scan_order|kmodes_" \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-kernels --no-extras > $O/ncu_launch.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:tc2_search_kernel -s 3 -c 1 \
     -o $O/tc2_search_full -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-kernels --no-extras > $O/ncu_tc2.log 2>&1
