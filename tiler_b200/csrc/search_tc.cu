@@ -24,6 +24,12 @@
 // position -> dataset row; the kernel translates when it writes its candidate lists.  k > 1 keeps the dataset
 // order and the norm MMA: near-identical rows (equal norms) would otherwise share one candidate list.
 //
+// Chained plan (tilesets beyond the L2).  One work item per query block lets the CTA pairs drift apart along the scan
+// until the operand streams from HBM for most of them.  The rows are then cut into L2-sized splits, the items run
+// split-major, and every item continues the candidate lists / ring and the threshold of its query block's previous
+// split (TcPlan.chain, search_tc.h; hand-over through per-block ready counters): same scan, same lists, the operand
+// read from HBM about once per pass instead of once per few query blocks.
+//
 // Exactness.  s~ + ||q~||^2 is the exact squared distance between the ROUNDED vectors up to
 // fp32 summation error, so by the triangle inequality every row that is not a candidate
 // has true distance >= (sqrt(tau + ||q~||^2 - a) - e)^2 with tau the final admission threshold,
