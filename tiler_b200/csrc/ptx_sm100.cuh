@@ -55,6 +55,31 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     }
 }
 
+// the same on a precomputed shared-memory address (hot loops: the generic -> shared conversion of a cluster kernel reads
+// SR_CgaCtaId, and under register pressure the compiler redoes it every iteration rather than keep the result)
+__device__ __forceinline__ bool mbar_try_wait_u32(uint32_t bar_addr, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}\n"
+        : "=r"(ok)
+        : "r"(bar_addr), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_u32(uint32_t bar_addr, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait_u32(bar_addr, parity)) {
+        if (++spins > (1u << 28)) __trap();
+    }
+}
+// a value the compiler must keep instead of recomputing (opaque move)
+__device__ __forceinline__ uint32_t keep_u32(uint32_t x) {
+    asm volatile("mov.u32 %0, %0;" : "+r"(x));
+    return x;
+}
+
 // ---- TMA ------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap *m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
