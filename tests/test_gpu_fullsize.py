@@ -138,3 +138,28 @@ def test_coherence_order_is_invisible(env, oracle, nq):
         got_i, got_e = i_tc[sel].cpu().numpy(), e_tc[sel].cpu().numpy()
         assert np.array_equal(got_i[solid], oi[solid, 0])
         assert np.allclose(got_e, od[:, 0], rtol=1e-5, atol=1e-7)
+
+
+def test_host_batch_larger_than_one_chunk_is_pipelined_and_consistent(env):
+    """ann_kdtree_search_batch with host buffers cuts a batch into chunks of 2^20 queries and uploads chunk i + 1 on
+    the copy stream under the search of chunk i (api.cu: search_batch_one).  Results of a ragged 2.2 M-query batch must
+    equal separate calls on slices that straddle the chunk boundaries, and a brute-force check on a sample."""
+    tb = env["tb"]
+    rng = np.random.default_rng(77)
+    n, dd, nq = 2048, 16, (1 << 21) + 100003
+    ds = rng.standard_normal((n, dd)).astype(np.float32)
+    q = rng.standard_normal((nq, dd)).astype(np.float32)
+    with tb.KDTree.from_rows(ds) as t:
+        for k in (1, 3):
+            idx, err = t.search_batch(q, k=k)
+            for lo, hi in [((1 << 20) - 300, (1 << 20) + 300), ((1 << 21) - 7, nq), (0, 1000)]:
+                i2, e2 = t.search_batch(q[lo:hi], k=k)
+                assert np.array_equal(idx[lo:hi], i2) and np.array_equal(err[lo:hi].view(np.uint32), e2.view(np.uint32))
+            sample = np.concatenate([np.arange(0, 64), np.arange((1 << 20) - 32, (1 << 20) + 32), np.arange(nq - 64, nq)])
+            d = ((q[sample, None, :].astype(np.float64) - ds[None, :, :].astype(np.float64)) ** 2).sum(-1)
+            want = np.argsort(d, axis=1, kind="stable")[:, :k]
+            gap = np.sort(d, axis=1)
+            clear = (gap[:, k] - gap[:, k - 1]) > 1e-5 * np.maximum(gap[:, k - 1], 1e-12)
+            if k == 1:
+                assert np.array_equal(idx.reshape(nq, -1)[sample][clear, 0], want[clear, 0])
+            assert np.allclose(err.reshape(nq, -1)[sample], np.sort(d, axis=1)[:, :k], rtol=1e-5, atol=1e-6)

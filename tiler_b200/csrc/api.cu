@@ -599,24 +599,57 @@ int tm_search_batch_dev(ANNkdtree *akd, const float *d_q, int64_t nq, int k, int
 }
 
 // one device: the batch goes through in chunks so that the temporaries stay bounded
+// Host batch on one device, in chunks of 2^20 queries.  More than one chunk: two input buffers, the upload of chunk
+// i + 1 rides on the device's copy stream under the search of chunk i (C5, 768 B per query: 15 ms of PCIe per 350 ms
+// chunk that were paid in full on the one stream).
 static int search_batch_one(ANNkdtree *akd, const float *h_q, int64_t nq, int k, int *h_idxs, float *h_errs) {
     InflightMark mark(akd);
     TM_API_GUARD_H(akd);
     int r = tm_ensure_device();
     if (r) return r;
     const int64_t chunk = std::min<int64_t>(nq, 1 << 20);
-    DevBuf q, i, e;
-    if ((r = q.alloc(sizeof(float) * (size_t)chunk * akd->dd))) return r;
+    const bool piped = nq > chunk;
+    const size_t row = sizeof(float) * (size_t)akd->dd;
+    DevBuf q[2], i, e;
+    if ((r = q[0].alloc(row * (size_t)chunk))) return r;
+    if (piped && (r = q[1].alloc(row * (size_t)chunk))) return r;
     if ((r = i.alloc(sizeof(int) * (size_t)chunk * k))) return r;
     if ((r = e.alloc(sizeof(float) * (size_t)chunk * k))) return r;
-    for (int64_t q0 = 0; q0 < nq; q0 += chunk) {
+    struct Events { // RAII: early returns must not leak them
+        cudaEvent_t in[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr}, ready = nullptr;
+        ~Events() { for (cudaEvent_t ev : {in[0], in[1], done[0], done[1], ready}) if (ev) cudaEventDestroy(ev); }
+    } ev;
+    cudaStream_t cs = g_stream;
+    if (piped) {
+        TmHostPath &hp = t_dev->hp;
+        if (!hp.cs) TM_CUDA(cudaStreamCreateWithFlags(&hp.cs, cudaStreamNonBlocking));
+        cs = hp.cs;
+        for (cudaEvent_t *p : {&ev.in[0], &ev.in[1], &ev.done[0], &ev.done[1], &ev.ready}) TM_CUDA(cudaEventCreateWithFlags(p, cudaEventDisableTiming));
+        TM_CUDA(cudaEventRecord(ev.ready, g_stream)); // the buffers come from the stream-ordered pool of g_stream
+        TM_CUDA(cudaStreamWaitEvent(cs, ev.ready, 0));
+    }
+    auto upload = [&](int64_t q0, int slot) -> int {
         const int64_t c = std::min<int64_t>(chunk, nq - q0);
-        TM_CUDA(cudaMemcpyAsync(q.p, h_q + q0 * akd->dd, sizeof(float) * (size_t)c * akd->dd, cudaMemcpyHostToDevice, g_stream));
-        if ((r = search_dev(akd, q.as<float>(), c, k, i.as<int>(), e.as<float>()))) return r;
+        if (piped) TM_CUDA(cudaStreamWaitEvent(cs, ev.done[slot], 0)); // the search that read this slot has finished (no-op at first)
+        TM_CUDA(cudaMemcpyAsync(q[slot].p, h_q + q0 * akd->dd, row * (size_t)c, cudaMemcpyHostToDevice, cs));
+        if (piped) TM_CUDA(cudaEventRecord(ev.in[slot], cs));
+        return 0;
+    };
+    if ((r = upload(0, 0))) return r;
+    int n = 0;
+    for (int64_t q0 = 0; q0 < nq; q0 += chunk, n++) {
+        const int64_t c = std::min<int64_t>(chunk, nq - q0);
+        const int slot = piped ? (n & 1) : 0;
+        if (piped && q0 + chunk < nq && (r = upload(q0 + chunk, slot ^ 1))) break;
+        if (piped) TM_CUDA(cudaStreamWaitEvent(g_stream, ev.in[slot], 0));
+        if ((r = search_dev(akd, q[slot].as<float>(), c, k, i.as<int>(), e.as<float>()))) break;
+        if (piped) TM_CUDA(cudaEventRecord(ev.done[slot], g_stream));
         TM_CUDA(cudaMemcpyAsync(h_idxs + q0 * k, i.p, sizeof(int) * (size_t)c * k, cudaMemcpyDeviceToHost, g_stream));
         if (h_errs) TM_CUDA(cudaMemcpyAsync(h_errs + q0 * k, e.p, sizeof(float) * (size_t)c * k, cudaMemcpyDeviceToHost, g_stream));
     }
-    return sync_out();
+    if (piped) cudaStreamSynchronize(cs); // nothing of this call may outlive its buffers, on error either
+    const int rs = sync_out();
+    return r ? r : rs;
 }
 
 int ann_kdtree_search_batch(ANNkdtree *akd, const float *h_q, int64_t nq, int k, int *h_idxs, float *h_errs) {
