@@ -580,12 +580,26 @@ def run_kmodes(args, rank, world, local_rank, name_wl):
     npnt, k = X.shape[0], cent.shape[0]
     value = npnt * args.steps / (ms / 1e3)
     # e2e: host buffers through tm_kmodes_assign (H2D of points + centroids, D2H of labels + dissimilarities)
-    Xh, Ch = Xl.cpu().numpy(), cent.cpu().numpy()
-    tb.kmodes_assign(Xh, Ch)
+    # (pinned host memory, caller-owned result buffers, the raw C-ABI call: what a compiled host pays)
+    import ctypes as _C
+    from tiler_b200._lib import lib as _l
+    Xp = torch.empty(Xl.shape, dtype=torch.uint8, pin_memory=True).copy_(Xl)
+    Cp = torch.empty(cent.shape, dtype=torch.uint8, pin_memory=True).copy_(cent)
+    cp = torch.empty(b - a, dtype=torch.int32, pin_memory=True)
+    dp = torch.empty(b - a, dtype=torch.int64, pin_memory=True)
+    torch.cuda.synchronize()
+    Xh, Ch, ch, dh = Xp.numpy(), Cp.numpy(), cp.numpy(), dp.numpy().view(np.uint64)
+    vp = _C.c_void_p
+
+    def host_call():
+        rc = _l.tm_kmodes_assign(vp(Xp.data_ptr()), b - a, vp(Cp.data_ptr()), cent.shape[0], tb.KM_ASM, vp(cp.data_ptr()), vp(dp.data_ptr()))
+        if rc:
+            raise RuntimeError(_l.tm_last_error().decode())
+    host_call()
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ch, dh = tb.kmodes_assign(Xh, Ch)
+        host_call()
     dt = time.perf_counter() - t0
     if world > 1:
         t = torch.tensor([dt], device=dev)

@@ -590,6 +590,8 @@ void tm_kmodes_scratch_free(TmKmScratch &c) {
     c = TmKmScratch();
 }
 
+TmKmScratch &g_km_scratch() { return g_km; }
+
 int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
                             int32_t *d_clust, uint64_t *d_dis, cudaStream_t s) {
     if (sem != TM_KM_ASM && sem != TM_KM_GENERIC) { tm_set_error("unknown KModes semantics %d", sem); return TM_EINVAL; }

@@ -205,6 +205,7 @@ int tm_search_tc(ANNkdtree *h, const float *d_q, int64_t nq, int k, int *d_idx, 
 int tm_launch_kmodes_assign(const uint8_t *d_X, int64_t np, const uint8_t *d_c, int64_t k, int sem,
                             int32_t *d_clust, uint64_t *d_dis, cudaStream_t s);
 int tm_kmodes_pack_centroids(TmKmScratch &c, const uint8_t *d_c, int64_t k, cudaStream_t s);
+TmKmScratch &g_km_scratch(); // the calling thread's device's scratch of the one-shot KModes calls (kmodes.cu)
 int tm_kmodes_update_packed(TmKmScratch &c, uint8_t *d_c, int64_t k, const uint8_t *d_rows, const int32_t *d_idx, int64_t m,
                             int *d_bad, cudaStream_t s);
 // optional completion through mapped host memory (KModes handle): merged results + the call's sequence number in *m_flag
