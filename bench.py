@@ -870,6 +870,44 @@ def run_b200(args, rank, world, local_rank):
         except Exception as ex:
             kernels = {"error": str(ex)[:200]}
 
+    # ---- N > 1: the one-GPU anchor of the strong-scaling curve, measured in the SAME run (rank 0 alone on the whole
+    # clip, the other GPUs idle behind a host-side barrier): the driver's N = 1 line is workload C2, not this one
+    anchor = None
+    if world > 1 and not args.no_extras:
+        dist.barrier(group=cpu_group)
+        if rank == 0:
+            try:
+                a_rgb, _ = lcg_queries(torch, qseed, 0, nq_total, tiles, pal, dev)
+                a_idx = torch.empty(nq_total * k, dtype=torch.int32, device=dev)
+                a_err = torch.empty(nq_total * k, dtype=torch.float32, device=dev)
+                a_q = None
+                if k > 1:
+                    a_q = torch.empty((nq_total, D), dtype=torch.float32, device=dev)
+                    tb.psyv_queries(a_rgb, out=a_q)
+
+                def whole_clip():
+                    if k == 1:
+                        sft.search_local(a_rgb, out_idx=a_idx, out_err=a_err)
+                    else:
+                        tree.search_batch(a_q, k, out_idx=a_idx, out_err=a_err)
+                whole_clip()
+                torch.cuda.synchronize()
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record(stream)
+                whole_clip()
+                a1.record(stream)
+                torch.cuda.synchronize()
+                a_ms = a0.elapsed_time(a1)
+                same = bool(torch.equal(a_idx[q0 * k:q1 * k], d_idx))  # rank 0's shard of the sharded run, bit for bit
+                anchor = {"n_gpus": 1, "workload": name_wl, "queries_total": nq_total, "value": nq_total / (a_ms / 1e3),
+                          "unit": "tile-queries/s", "ms_per_step": a_ms, "steps": 1, "warmup": 1,
+                          "rank0_shard_equal_to_sharded_run": same,
+                          "note": "rank 0 alone on the whole clip after the timed region, inputs resident in HBM, CUDA events"}
+                del a_rgb, a_idx, a_err, a_q
+            except Exception as ex:
+                anchor = {"error": str(ex)[:300]}
+        dist.barrier(group=cpu_group)
+
     # ---- e2e for N > 1: ONE process (rank 0) drives all N GPUs through the C ABI (tm_set_devices), host buffers
     single = None
     if world > 1 and not args.no_e2e:
@@ -944,6 +982,8 @@ def run_b200(args, rank, world, local_rank):
             line["e2e"] = e2e
         if world > 1 and e2e_pp:
             line["e2e_process_per_gpu"] = e2e_pp
+        if anchor:
+            line["strong_scaling_anchor_1gpu"] = anchor
         if single and "error" in single:
             line["e2e_single_process_error"] = single["error"]
         if kernels:
