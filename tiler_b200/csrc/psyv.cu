@@ -98,13 +98,15 @@ __device__ __forceinline__ void dct_plane(const double (&a)[64], const double *l
 //      doubles = 4 banks apart -> conflict free), runs the Haar / DCT, and stages the float row in the same
 //      shared memory (dead by then) for a coalesced 16-byte store.
 constexpr int PQ_TILES = 32;
-constexpr int PQ_THREADS = 96;
+constexpr int PQ_THREADS = 96;   // DCT branch: thread = (tile, plane)
+constexpr int PQ_THREADS_W = 192; // wavelet branch: thread = (tile, plane, row half), see haar_half below
+__host__ __device__ constexpr int pq_threads(bool wavelets, bool split) { return wavelets && split ? PQ_THREADS_W : PQ_THREADS; }
 constexpr int PQ_CPN_STRIDE = 66;  // doubles per (plane, tile) row
 constexpr int PQ_OUT_STRIDE = 196; // words per staged output row (192 + 4)
 constexpr size_t PQ_CPN_BYTES = (size_t)3 * PQ_TILES * PQ_CPN_STRIDE * 8;
 constexpr size_t PQ_SMEM_LINEAR = PQ_CPN_BYTES;
 constexpr size_t PQ_SMEM_LUT = PQ_CPN_BYTES + 256 * 8;
-static_assert((size_t)PQ_TILES * PQ_OUT_STRIDE * 4 <= PQ_CPN_BYTES, "output staging aliases the component buffer");
+static_assert((size_t)PQ_TILES * PQ_OUT_STRIDE * 4 + (size_t)PQ_THREADS_W * 16 <= PQ_CPN_BYTES, "output staging + the halves' exchange area alias the component buffer");
 
 // Optional second output of the query kernel: the tensor-core engine's centred fp16 operand and the two norms
 // the certificate needs (what search_tc.cu's operand_kernel derives from the float rows), written from the
@@ -135,8 +137,71 @@ __device__ __forceinline__ void store_row_smem(float *dst, const double (&a)[64]
         d4[i] = make_float4((float)a[4 * i], (float)a[4 * i + 1], (float)a[4 * i + 2], (float)a[4 * i + 3]);
 }
 
-template <bool WAVELETS, bool LINEAR>
-__global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t *__restrict__ rgb, int64_t nq,
+// The 3-level Haar of one 8 x 8 plane split over TWO threads by row halves (hf = 0: input rows 0-3, hf = 1: rows 4-7),
+// 32 doubles each instead of 64: ~100 registers instead of 168, i.e. 18-24 warps per SM instead of 12 for a kernel whose
+// pipes are all under half busy at 12.  Same operations on the same operands in the same order as
+// haar_level (WaveletGS, main.pas:2805-2840) - every output is one (p + q) * f or (p - q) * f of the same p, q - so the
+// rows stay bit-identical.  A row pass is local to a row; a column pass pairs rows (2y, 2y + 1), which one thread owns
+// at level 8 (its rows 0-1 and 2-3) and at level 4 (the two low rows it has just produced); only the level-2 column
+// pass pairs a row of one half with a row of the other: two values change hands through shared memory.
+// After the call, with S = the thread's four 8-wide rows:  S0[0..3] = coefficient row hf, S0[4..7] = row 2 hf (cols 4-7),
+// S1[0..3] = row 2 + hf, S1[4..7] = row 2 hf + 1 (cols 4-7), S2 = row 4 + 2 hf, S3 = row 5 + 2 hf.
+__device__ __forceinline__ void haar_rows(double (&r)[8], int n, double f) {
+    // n = 8 or 4 or 2 leading values of the row, in place
+    double t[8];
+#pragma unroll
+    for (int x = 0; x < 4; x++)
+        if (x < n / 2) {
+            const double p = r[2 * x], q = r[2 * x + 1];
+            t[x] = (p + q) * f;
+            t[x + n / 2] = (p - q) * f;
+        }
+#pragma unroll
+    for (int x = 0; x < 8; x++)
+        if (x < n) r[x] = t[x];
+}
+__device__ __forceinline__ void haar_half(double (&S)[4][8], int hf, double f, double *xch_mine, const double *xch_other) {
+    // level 8: rows, then the column pairs (S0, S1) and (S2, S3); low rows to S0, S1, high rows to S2, S3
+#pragma unroll
+    for (int y = 0; y < 4; y++) haar_rows(S[y], 8, f);
+#pragma unroll
+    for (int x = 0; x < 8; x++) {
+        const double p0 = S[0][x], q0 = S[1][x], p1 = S[2][x], q1 = S[3][x];
+        S[0][x] = (p0 + q0) * f;
+        S[2][x] = (p0 - q0) * f;
+        S[1][x] = (p1 + q1) * f;
+        S[3][x] = (p1 - q1) * f;
+    }
+    // level 4 on the low rows' first four columns: rows, then the column pair (S0, S1)
+    haar_rows(S[0], 4, f);
+    haar_rows(S[1], 4, f);
+#pragma unroll
+    for (int x = 0; x < 4; x++) {
+        const double p = S[0][x], q = S[1][x];
+        S[0][x] = (p + q) * f;
+        S[1][x] = (p - q) * f;
+    }
+    // level 2 on coefficient rows 0 (half 0's S0) and 1 (half 1's S0), columns 0-1: row pass, exchange, column pass
+    haar_rows(S[0], 2, f);
+    xch_mine[0] = S[0][0];
+    xch_mine[1] = S[0][1];
+    __syncthreads();
+    const double o0 = xch_other[0], o1 = xch_other[1];
+    if (hf == 0) { // p = row 0 (mine), q = row 1 (the other half's): the low row stays here
+        S[0][0] = (S[0][0] + o0) * f;
+        S[0][1] = (S[0][1] + o1) * f;
+    } else {       // p = row 0 (the other half's), q = row 1 (mine): the high row stays here
+        S[0][0] = (o0 - S[0][0]) * f;
+        S[0][1] = (o1 - S[0][1]) * f;
+    }
+}
+
+// SPLIT: the two-threads-per-plane wavelet path.  Used when the kernel also writes the tensor-core operand (the fused
+// variant the FrameTiling path runs: 24 instead of 12 warps per SM hide the operand phase, descriptor phase of a C2 step
+// 3.77 -> 3.41 ms); the plain descriptor call keeps one thread per plane (0.69 ms per 2 M tiles against 0.90 ms split:
+// alone, the extra index arithmetic of twice the threads costs more than the occupancy buys).
+template <bool WAVELETS, bool LINEAR, bool SPLIT>
+__global__ void __launch_bounds__(pq_threads(WAVELETS, SPLIT)) psyv_queries_kernel(const int32_t *__restrict__ rgb, int64_t nq,
                                                                    const PsyvTables *__restrict__ tabs,
                                                                    PsyvConsts K, const double *__restrict__ lut,
                                                                    const double *__restrict__ qw,
@@ -145,6 +210,8 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
     double *cpn = reinterpret_cast<double *>(psm);
     double *ftab = reinterpret_cast<double *>(psm + PQ_CPN_BYTES);
     float *sout = reinterpret_cast<float *>(psm);
+    constexpr int NT = pq_threads(WAVELETS, SPLIT);
+    double *xch = reinterpret_cast<double *>(psm + (size_t)PQ_TILES * PQ_OUT_STRIDE * 4); // behind the output staging
     __shared__ int64_t dst_row[PQ_TILES]; // output row of each of the block's tiles
     const int64_t q0 = (int64_t)blockIdx.x * PQ_TILES;
     const int ntile = (int)min((int64_t)PQ_TILES, nq - q0);
@@ -155,11 +222,11 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
     {   // pixel phase (FromRGB main.pas:571-576, RGBToYUV main.pas:2662-2677); all of a thread's pixels are
         // requested before the first one is used (22 independent loads in flight per thread)
         const int32_t *src = rgb + q0 * 64;
-        constexpr int PER_THREAD = (PQ_TILES * 64 + PQ_THREADS - 1) / PQ_THREADS;
+        constexpr int PER_THREAD = (PQ_TILES * 64 + NT - 1) / NT;
         int32_t colv[PER_THREAD];
 #pragma unroll
         for (int k = 0; k < PER_THREAD; k++) {
-            const int e = threadIdx.x + k * PQ_THREADS;
+            const int e = threadIdx.x + k * NT;
             colv[k] = e < ntile * 64 ? __ldg(src + e) : 0;
         }
         // destination rows: requested together with the pixels (no dependent load), used only by the stores
@@ -167,7 +234,7 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
             dst_row[threadIdx.x] = (int)threadIdx.x < ntile ? (op.dst ? (int64_t)__ldg(op.dst + q0 + threadIdx.x) : q0 + threadIdx.x) : 0;
 #pragma unroll
         for (int k = 0; k < PER_THREAD; k++) {
-            const int e = threadIdx.x + k * PQ_THREADS;
+            const int e = threadIdx.x + k * NT;
             if (e < ntile * 64) {
                 const int32_t col = colv[k];
                 const double fr = channel_value<LINEAR>(col & 0xff, ftab, K.rcp255);
@@ -184,43 +251,75 @@ __global__ void __launch_bounds__(PQ_THREADS) psyv_queries_kernel(const int32_t 
         }
     }
     __syncthreads();
-    // lanes of a warp take consecutive tiles of ONE plane (96 threads = 3 planes x 32 tiles)
-    const int plane = threadIdx.x / PQ_TILES, tl = threadIdx.x % PQ_TILES;
-    double a[64];
-    if (tl < ntile) {
-        const double2 *src = reinterpret_cast<const double2 *>(cpn + (plane * PQ_TILES + tl) * PQ_CPN_STRIDE);
+    if (WAVELETS && SPLIT) {
+        // lanes of a warp take consecutive tiles; warp = (plane, row half): 192 threads = 3 planes x 2 halves x 32 tiles
+        const int tl = threadIdx.x & 31, plane = threadIdx.x >> 6, hf = (threadIdx.x >> 5) & 1;
+        double S[4][8];
+        if (tl < ntile) {
+            const double2 *src = reinterpret_cast<const double2 *>(cpn + (plane * PQ_TILES + tl) * PQ_CPN_STRIDE + hf * 32);
 #pragma unroll
-        for (int i = 0; i < 32; i++) {
-            const double2 v = src[i];
-            a[2 * i] = v.x;
-            a[2 * i + 1] = v.y;
-        }
-    }
-    __syncthreads(); // every component row is in registers: the buffer becomes the output staging
-    if (tl < ntile) {
-        float *dst = sout + tl * PQ_OUT_STRIDE + plane * 64;
-        if (WAVELETS) {
-            haar_level<8>(a, K.haar);
-            haar_level<4>(a, K.haar);
-            haar_level<2>(a, K.haar);
-            store_row_smem(dst, a);
+            for (int i = 0; i < 16; i++) {
+                const double2 v = src[i];
+                S[i >> 2][2 * (i & 3)] = v.x;
+                S[i >> 2][2 * (i & 3) + 1] = v.y;
+            }
         } else {
-            dct_plane(a, lut, qw, plane, dst);
+#pragma unroll
+            for (int y = 0; y < 4; y++)
+#pragma unroll
+                for (int x = 0; x < 8; x++) S[y][x] = 0.0;
+        }
+        __syncthreads(); // every component row is in registers: the buffer becomes the output staging + exchange area
+        haar_half(S, hf, K.haar, xch + 2 * threadIdx.x, xch + 2 * (threadIdx.x ^ 32)); // (contains one __syncthreads)
+        if (tl < ntile) {
+            float *dst = sout + tl * PQ_OUT_STRIDE + plane * 64;
+            auto st4 = [&](int row, int col, const double *v) {
+                *reinterpret_cast<float4 *>(dst + row * 8 + col) = make_float4((float)v[0], (float)v[1], (float)v[2], (float)v[3]);
+            };
+            st4(hf, 0, &S[0][0]);          st4(2 * hf, 4, &S[0][4]);
+            st4(2 + hf, 0, &S[1][0]);      st4(2 * hf + 1, 4, &S[1][4]);
+            st4(4 + 2 * hf, 0, &S[2][0]);  st4(4 + 2 * hf, 4, &S[2][4]);
+            st4(5 + 2 * hf, 0, &S[3][0]);  st4(5 + 2 * hf, 4, &S[3][4]);
+        }
+    } else {
+        // lanes of a warp take consecutive tiles of ONE plane (96 threads = 3 planes x 32 tiles)
+        const int plane = threadIdx.x / PQ_TILES, tl = threadIdx.x % PQ_TILES;
+        double a[64];
+        if (tl < ntile) {
+            const double2 *src = reinterpret_cast<const double2 *>(cpn + (plane * PQ_TILES + tl) * PQ_CPN_STRIDE);
+#pragma unroll
+            for (int i = 0; i < 32; i++) {
+                const double2 v = src[i];
+                a[2 * i] = v.x;
+                a[2 * i + 1] = v.y;
+            }
+        }
+        __syncthreads(); // every component row is in registers: the buffer becomes the output staging
+        if (tl < ntile) {
+            float *dst = sout + tl * PQ_OUT_STRIDE + plane * 64;
+            if (WAVELETS) {
+                haar_level<8>(a, K.haar);
+                haar_level<4>(a, K.haar);
+                haar_level<2>(a, K.haar);
+                store_row_smem(dst, a);
+            } else {
+                dct_plane(a, lut, qw, plane, dst);
+            }
         }
     }
     __syncthreads();
     {   // coalesced store of the block's rows (48 float4 per row; rows are contiguous unless op.dst scatters them)
-        for (int e = threadIdx.x; e < ntile * 48; e += PQ_THREADS) {
+        for (int e = threadIdx.x; e < ntile * 48; e += NT) {
             const int t = e / 48, j = e - t * 48;
             reinterpret_cast<float4 *>(out + dst_row[t] * TM_DCT)[j] = *reinterpret_cast<const float4 *>(sout + t * PQ_OUT_STRIDE + j * 4);
         }
     }
-    if (op.q16) { // 16 lanes per row, 3 float4 each; six rows per pass (trip count uniform: shuffles need full warps)
+    if (op.q16) { // 16 lanes per row, 3 float4 each; NT / 16 rows per pass (trip count uniform: shuffles need full warps)
         const int l16 = threadIdx.x & 15, grp = threadIdx.x >> 4;
         const float4 *mean4 = reinterpret_cast<const float4 *>(op.mean);
 #pragma unroll 1
-        for (int i = 0; i < (PQ_TILES + 5) / 6; i++) {
-            const int t = grp + 6 * i;
+        for (int i = 0; i < (PQ_TILES + NT / 16 - 1) / (NT / 16); i++) {
+            const int t = grp + (NT / 16) * i;
             float s16 = 0.f, sex = 0.f, sde = 0.f;
             if (t < ntile) {
                 uint2 *drow = reinterpret_cast<uint2 *>(op.q16 + dst_row[t] * TM_DCT);
@@ -587,23 +686,30 @@ int tm_launch_psyv_queries_operand(const int32_t *d_rgb, int64_t nq, int flags, 
     const double *qw = (flags & TM_PSYV_QWEIGHT) ? g_ps.qw : nullptr;
     static std::atomic<uint32_t> attr{0}; // per device (tm_first_on_device)
     if (tm_first_on_device(attr)) {
-        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
-        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
-        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
-        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LINEAR));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
+        TM_CUDA(cudaFuncSetAttribute(psyv_queries_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PQ_SMEM_LUT));
     }
     const bool linear = gamma < 0 && g_ps.linear_ok; // GammaCor = -1: c / 255.0 without the table
     const bool wav = (flags & TM_PSYV_WAVELETS) != 0;
+    const bool split = wav && d_q16 != nullptr; // fused operand: two threads per plane (see the kernel)
     const PsyvTables *tabs = g_ps.tabs[gamma + 1];
     const PsyvOperandOut op{d_mean, static_cast<__half *>(d_q16), d_qn16, d_qne, d_qde, d_dst};
-    if (wav && linear)
-        psyv_queries_kernel<true, true><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+    if (wav && linear && split)
+        psyv_queries_kernel<true, true, true><<<grid, PQ_THREADS_W, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+    else if (wav && linear)
+        psyv_queries_kernel<true, true, false><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+    else if (wav && split)
+        psyv_queries_kernel<true, false, true><<<grid, PQ_THREADS_W, PQ_SMEM_LUT, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     else if (wav)
-        psyv_queries_kernel<true, false><<<grid, PQ_THREADS, PQ_SMEM_LUT, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+        psyv_queries_kernel<true, false, false><<<grid, PQ_THREADS, PQ_SMEM_LUT, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     else if (linear)
-        psyv_queries_kernel<false, true><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+        psyv_queries_kernel<false, true, false><<<grid, PQ_THREADS, PQ_SMEM_LINEAR, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     else
-        psyv_queries_kernel<false, false><<<grid, PQ_THREADS, PQ_SMEM_LUT, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
+        psyv_queries_kernel<false, false, false><<<grid, PQ_THREADS, PQ_SMEM_LUT, s>>>(d_rgb, nq, tabs, K, g_ps.lut, qw, d_out, op);
     tm_count_launch();
     return tm_check(cudaGetLastError(), "psyv_queries_kernel");
 }
